@@ -1,0 +1,148 @@
+"""Synthetic inputs for the compute-graph solve: images, the minibatch index, topologies and
+level-synchronous D-PSGD compute graphs in the reference's serialized task format.
+
+The reference draws real CIFAR-10 partitions through flwr_datasets (network) and a fresh shuffled
+`DataLoader` per train call (`dasklearn/model_trainer.py:87`).  Here every node owns a fixed
+uint8 HWC partition and each (node, round) gets a scripted permutation, so the CUDA path and
+the CPU oracle consume identical minibatches.
+"""
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+
+def make_images(n: int, hw: int, c: int, num_classes: int, seed: int = 1234, mix: float = 0.6
+                ) -> Tuple[np.ndarray, np.ndarray]:
+    """uint8 HWC images `[n, hw, hw, c]` and int64 labels; class prototype blended with noise."""
+    rs = np.random.RandomState(seed)
+    protos = rs.randint(0, 256, size=(num_classes, hw, hw, c)).astype(np.float32)
+    labels = rs.randint(0, num_classes, size=(n,)).astype(np.int64)
+    noise = rs.randint(0, 256, size=(n, hw, hw, c)).astype(np.float32)
+    img = np.clip(mix * protos[labels] + (1.0 - mix) * noise, 0, 255).astype(np.uint8)
+    return img, labels
+
+
+def make_partitions(n_nodes: int, n_i: int, hw: int, c: int, num_classes: int, seed: int = 1234,
+                    mix: float = 0.6) -> Tuple[np.ndarray, np.ndarray]:
+    """Per-node train partitions: images `[n_nodes, n_i, hw, hw, c]` uint8, labels `[n_nodes, n_i]`.
+    Train and test share prototypes because both come from `make_images` with the same seed
+    stream prefix (prototypes are drawn first)."""
+    img, lab = make_images(n_nodes * n_i, hw, c, num_classes, seed, mix)
+    return img.reshape(n_nodes, n_i, hw, hw, c), lab.reshape(n_nodes, n_i)
+
+
+def make_test_split(n_test: int, hw: int, c: int, num_classes: int, seed: int = 1234,
+                    mix: float = 0.6) -> Tuple[np.ndarray, np.ndarray]:
+    rs = np.random.RandomState(seed)
+    protos = rs.randint(0, 256, size=(num_classes, hw, hw, c)).astype(np.float32)
+    rs2 = np.random.RandomState(seed + 7919)
+    labels = rs2.randint(0, num_classes, size=(n_test,)).astype(np.int64)
+    noise = rs2.randint(0, 256, size=(n_test, hw, hw, c)).astype(np.float32)
+    img = np.clip(mix * protos[labels] + (1.0 - mix) * noise, 0, 255).astype(np.uint8)
+    return img, labels
+
+
+def minibatch_permutation(seed: int, node: int, round_nr: int, n_i: int) -> np.ndarray:
+    """The scripted sample order a node's DataLoader yields in `round_nr` (stand-in for the
+    `shuffle=True` permutation of `dasklearn/model_trainer.py:87`)."""
+    rs = np.random.RandomState((seed * 1000003 + node * 1009 + round_nr) % (2 ** 31 - 1))
+    return rs.permutation(n_i).astype(np.int32)
+
+
+def minibatch_index(seed: int, nodes: Sequence[int], rounds: Sequence[int], n_i: int, batch: int,
+                    local_steps: int) -> Tuple[np.ndarray, np.ndarray]:
+    """`idx[t, step, slot]` (sample id inside the node's partition, -1 = empty slot) and
+    `count[t, step]`.  Steps executed = min(local_steps, ceil(n_i / batch)) and the last batch may
+    be partial, exactly like the reference loop (`dasklearn/model_trainer.py:99-102`)."""
+    T = len(nodes)
+    idx = -np.ones((T, local_steps, batch), dtype=np.int32)
+    cnt = np.zeros((T, local_steps), dtype=np.int32)
+    for t, (node, rnd) in enumerate(zip(nodes, rounds)):
+        perm = minibatch_permutation(seed, node, rnd, n_i)
+        for s in range(local_steps):
+            chunk = perm[s * batch:(s + 1) * batch]
+            if len(chunk) == 0:
+                break
+            idx[t, s, :len(chunk)] = chunk
+            cnt[t, s] = len(chunk)
+    return idx, cnt
+
+
+# ---------------------------------------------------------------------------------------------
+# Topologies and compute graphs
+# ---------------------------------------------------------------------------------------------
+
+def kreg_topology(n: int, k: int, seed: int) -> List[List[int]]:
+    """In-neighbour lists of the `kreg` topology (`dasklearn/simulation/dpsgd/simulation.py:35-36`:
+    `nx.random_regular_graph(k, N, seed).to_directed()`)."""
+    import networkx as nx
+    g = nx.random_regular_graph(k, n, seed=seed).to_directed()
+    return [sorted(g.predecessors(i)) for i in range(n)]
+
+
+def ring_topology(n: int) -> List[List[int]]:
+    return [[(i - 1) % n, (i + 1) % n] for i in range(n)]
+
+
+def exponential_topology(n: int) -> List[List[int]]:
+    """Directed exponential graph i -> (i + 2^j) mod n; not in the reference, provided
+    as the C5 extension.  Returns in-neighbour lists."""
+    preds: List[List[int]] = [[] for _ in range(n)]
+    j = 1
+    while j < n:
+        for i in range(n):
+            d = (i + j) % n
+            if i not in preds[d] and d != i:
+                preds[d].append(i)
+        j *= 2
+    return preds
+
+
+def dpsgd_dag(n: int, rounds: int, in_neighbours: List[List[int]], test_interval: int = 0,
+              name_offset: int = 0, order_seed: Optional[int] = None) -> List[Dict]:
+    """Serialized D-PSGD compute graph (list of task dicts, the `WorkflowDAG.serialize()` format of
+    `dasklearn/tasks/dag.py:28-32` / `dasklearn/tasks/task.py:59-66`) for a fixed topology with
+    every node online: per round N `train` tasks then N `aggregate` tasks whose `models` list is
+    in-neighbours (arrival order) followed by the node's own model
+    (`dasklearn/simulation/dpsgd/client.py:145`), plus `test_<peer>_<round>` pass-through tasks
+    every `test_interval` rounds (:153-159).  Arrival order is the sorted neighbour order unless
+    `order_seed` shuffles it per aggregate."""
+    rs = np.random.RandomState(order_seed) if order_seed is not None else None
+    tasks: Dict[str, Dict] = {}
+    counter = {"train": name_offset, "agg": name_offset}
+    outputs: Dict[str, List[Tuple[str, int]]] = {}
+
+    def add(name, func, data, inputs):
+        tasks[name] = {"name": name, "func": func, "data": data,
+                       "inputs": list(inputs), "outputs": []}
+        for src, idx in inputs:
+            tasks[src]["outputs"].append((name, idx))
+
+    model_of: List[Tuple[Optional[str], int]] = [(None, 0)] * n
+    t_us = 0
+    for r in range(1, rounds + 1):
+        trained: List[Tuple[str, int]] = []
+        for peer in range(n):
+            counter["train"] += 1
+            name = "train_%d" % counter["train"]
+            prev = model_of[peer]
+            add(name, "train", {"model": prev, "round": r, "time": t_us, "peer": peer},
+                [] if prev[0] is None else [prev])
+            trained.append((name, 0))
+        t_us += 3_000_000
+        for peer in range(n):
+            nbs = list(in_neighbours[peer])
+            if rs is not None:
+                rs.shuffle(nbs)
+            models = [trained[j] for j in nbs] + [trained[peer]]
+            counter["agg"] += 1
+            name = "agg_%d" % counter["agg"]
+            add(name, "aggregate", {"models": list(models), "round": r, "peer": peer}, models)
+            model_of[peer] = (name, 0)
+            if test_interval > 0 and r % test_interval == 0:
+                tname = "test_%d_%d" % (peer, r)
+                add(tname, "test", {"model": (name, 0), "round": r, "time": t_us, "peer": peer},
+                    [(name, 0)])
+                model_of[peer] = (tname, 0)
+        t_us += 1_000_000
+    return list(tasks.values())

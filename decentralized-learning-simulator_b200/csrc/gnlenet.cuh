@@ -1,0 +1,72 @@
+// GNLeNet (reference: dasklearn/models/cifar10.py:103-142) — constants, workspace carving and the
+// kernel-launch interface shared by the train / grad / eval entry points.
+#pragma once
+#include "common.cuh"
+
+namespace dls {
+namespace gnl {
+
+constexpr int P = DLS_GNLENET_P;
+// flat parameter offsets in parameters() order
+constexpr int OFF_W1 = 0, OFF_B1 = 2400, OFF_G1W = 2432, OFF_G1B = 2464;
+constexpr int OFF_W2 = 2496, OFF_B2 = 28096, OFF_G2W = 28128, OFF_G2B = 28160;
+constexpr int OFF_W3 = 28192, OFF_B3 = 79392, OFF_G3W = 79456, OFF_G3B = 79520;
+constexpr int OFF_FCW = 79584, OFF_FCB = 85344;
+
+constexpr int IMG = 32, IMG_C = 3, IMG_BYTES = IMG * IMG * IMG_C;
+constexpr int C1 = 32, H1 = 32, PH1 = 15;     // conv1 out 32x32x32 -> pool -> 15x15x32
+constexpr int C2 = 32, H2 = 15, PH2 = 7;      // conv2 out 15x15x32 -> pool -> 7x7x32
+constexpr int C3 = 64, H3 = 7, PH3 = 3;       // conv3 out 7x7x64   -> pool -> 3x3x64
+constexpr int NCLS = 10, FEAT = 576;
+constexpr float GN_EPS = 1e-5f;
+
+constexpr int A1_SZ = PH1 * PH1 * C1;   // 7200
+constexpr int C2_SZ = H2 * H2 * C2;     // 7200
+constexpr int A2_SZ = PH2 * PH2 * C2;   // 1568
+constexpr int C3_SZ = H3 * H3 * C3;     // 3136
+constexpr int A3_SZ = PH3 * PH3 * C3;   // 576
+constexpr int GNP_SZ = 2 * (C1 + C2 + C3);   // per-slot partial GN parameter gradients (256)
+
+constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
+constexpr int PREP_SZ = 2 * W2T_SZ + 2 * W3T_SZ;   // W2t, W2d, W3t, W3d per model
+
+// All activations are NHWC fp32, one contiguous record per sample slot.
+struct Workspace {
+    // forward (kept for backward)
+    float *p1, *a1, *c2, *a2, *c3, *a3;
+    float *st1, *st2, *st3;              // [slot][4] = mean0, rstd0, mean1, rstd1
+    uint8_t *idx1, *idx2, *idx3;         // arg-max position inside the 3x3 window (0..8)
+    // backward
+    float *da3, *dc3, *da2, *dc2, *da1, *dp1, *gnp;
+    float *G;                            // [n_groups][ldg] gradient rows (train) — may point to user memory
+    int64_t ldg;
+    float *prep;                         // [n_models][PREP_SZ]
+    float *glog;                         // [n_groups][2] loss sum, correct count (eval) / loss (train)
+    int32_t *desc_i32;                   // scratch for generated descriptors (eval)
+};
+
+struct Pass {
+    int n_groups, gs, n_models;
+    const int32_t *gmodel;     // [n_groups] model index, nullptr = identity
+    const int32_t *mrow;       // [n_models] row of X
+    const int32_t *img_idx;    // [n_groups*gs] global image id, -1 = empty slot
+    const int32_t *gcount;     // [n_groups] active slots per group (mean-loss divisor)
+    const uint8_t *images;
+    const int64_t *labels;
+    const float *X;
+    int64_t ldx;
+};
+
+int64_t workspace_bytes(int n_groups, int gs, int n_models, bool backward, bool own_G);
+// Carves `base`; returns bytes used.
+int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, bool backward, bool own_G);
+
+int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);
+int forward(const Pass &p, Workspace &ws, bool save_for_backward, cudaStream_t st);
+// mode 0: train (writes dlogits-derived grads: needs backward buffers); mode 1: eval
+int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *out_logits,
+               int logits_stride_model, cudaStream_t st);
+int backward(const Pass &p, Workspace &ws, cudaStream_t st);
+
+}  // namespace gnl
+}  // namespace dls

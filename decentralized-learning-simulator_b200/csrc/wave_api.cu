@@ -1,0 +1,220 @@
+// C-ABI entry points for the train / grad / test waves (see include/dls_b200.h).
+#include "gnlenet.cuh"
+
+namespace dls {
+
+// Fused optimizer update over the wave's rows — torch.optim.SGD semantics
+// (reference: dasklearn/optimizer/sgd.py:4-14; state carry-over dasklearn/model_trainer.py:89-92):
+//   g += wd * p;  buf = g (node's first ever step) else buf = mu * buf + g;  p -= lr * buf
+// grid = (column blocks, n_tasks).
+__global__ void __launch_bounds__(256)
+sgd_update_kernel(float *__restrict__ X, int64_t ldx, float *__restrict__ M, int64_t ldm,
+                  const float *__restrict__ G, int64_t ldg, const int32_t *__restrict__ task_row,
+                  const int32_t *__restrict__ task_peer, const uint8_t *__restrict__ first,
+                  const int32_t *__restrict__ gcount, int64_t P, float lr, float mu, float wd)
+{
+    const int g = blockIdx.y;
+    if (gcount[g] <= 0) return;
+    float *x = X + (int64_t)task_row[g] * ldx;
+    const float *gr = G + (int64_t)g * ldg;
+    float *mb = (M && mu != 0.f) ? M + (int64_t)task_peer[g] * ldm : nullptr;
+    const bool fst = first ? (first[g] != 0) : false;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        float gv = gr[i];
+        const float pv = x[i];
+        if (wd != 0.f) gv = fmaf(wd, pv, gv);
+        if (mb) {
+            const float b = fst ? gv : __fadd_rn(__fmul_rn(mb[i], mu), gv);
+            mb[i] = b;
+            gv = b;
+        }
+        x[i] = fmaf(-lr, gv, pv);
+    }
+}
+
+__global__ void eval_desc_kernel(int32_t *gmodel, int32_t *img_idx, int32_t *gcount, int g0, int n_groups,
+                                 int gs, int gpm, int n_test)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_groups * gs) return;
+    const int gl = i / gs, j = i - gl * gs, g = g0 + gl;
+    const int m = g / gpm, chunk = g - m * gpm;
+    const int sample = chunk * gs + j;
+    img_idx[i] = sample < n_test ? sample : -1;
+    if (j == 0) {
+        gmodel[gl] = m;
+        const int rem = n_test - chunk * gs;
+        gcount[gl] = rem < gs ? (rem > 0 ? rem : 0) : gs;
+    }
+}
+
+// Sum per-group eval results of each model in group order (deterministic, fp64).
+__global__ void eval_reduce_kernel(const float *glog_all, int gpm, int n_models, int32_t *out_correct,
+                                   double *out_loss)
+{
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_models) return;
+    double ls = 0.0;
+    int hs = 0;
+    for (int k = 0; k < gpm; ++k) {
+        ls += (double)glog_all[((int64_t)m * gpm + k) * 2];
+        hs += (int)glog_all[((int64_t)m * gpm + k) * 2 + 1];
+    }
+    out_loss[m] = ls;
+    out_correct[m] = hs;
+}
+
+constexpr int EVAL_GS = 32;
+constexpr int EVAL_CHUNK_GROUPS = 512;   // 16384 sample slots per pass
+
+}  // namespace dls
+
+using namespace dls;
+
+static int check_rows(const void *X, int64_t ld, int64_t P)
+{
+    if (!X) return DLS_E_ARG;
+    if (!aligned16(X) || ld % 4) return DLS_E_ALIGN;
+    if (ld < P) return DLS_E_SHAPE;
+    return 0;
+}
+
+extern "C" int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int32_t batch)
+{
+    if (n_tasks < 0 || batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
+    if (arch == DLS_ARCH_GNLENET) return gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true);
+    return DLS_E_SHAPE;
+}
+
+static int gnl_step(const gnl::Pass &p, gnl::Workspace &ws, float *loss_out, cudaStream_t st)
+{
+    int rc;
+    if ((rc = gnl::prep_weights(p, ws, true, st))) return rc;
+    if ((rc = gnl::forward(p, ws, true, st))) return rc;
+    if ((rc = gnl::classifier(p, ws, 0, loss_out, nullptr, 0, st))) return rc;
+    if ((rc = gnl::backward(p, ws, st))) return rc;
+    return 0;
+}
+
+extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int64_t ldm,
+                              const int32_t *task_row, const int32_t *task_peer,
+                              const uint8_t *mom_first, const uint8_t *images, const int64_t *labels,
+                              const int32_t *mb_index, const int32_t *mb_count, int32_t n_tasks,
+                              int32_t n_steps, int32_t batch, float lr, float mu, float wd,
+                              float *loss_out, int32_t precision, void *workspace,
+                              int64_t workspace_bytes, void *stream)
+{
+    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (precision != 0) return DLS_E_SHAPE;
+    if (!task_row || !task_peer || !images || !labels || !mb_index || !mb_count || !workspace ||
+        n_tasks < 0 || n_steps < 0)
+        return DLS_E_ARG;
+    if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
+    int rc = check_rows(X, ldx, gnl::P);
+    if (rc) return rc;
+    if (mu != 0.f) {
+        if ((rc = check_rows(M, ldm, gnl::P))) return rc;
+        if (!mom_first) return DLS_E_ARG;
+    }
+    if (n_tasks == 0 || n_steps == 0) return 0;
+    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true)) return DLS_E_WS;
+    cudaStream_t st = (cudaStream_t)stream;
+    gnl::Workspace ws;
+    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, true);
+    for (int s = 0; s < n_steps; ++s) {
+        gnl::Pass p;
+        p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks;
+        p.gmodel = nullptr; p.mrow = task_row;
+        p.img_idx = mb_index + (int64_t)s * n_tasks * batch;
+        p.gcount = mb_count + (int64_t)s * n_tasks;
+        p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
+        if ((rc = gnl_step(p, ws, loss_out ? loss_out + (int64_t)s * n_tasks : nullptr, st))) return rc;
+        dim3 grid(32, n_tasks);
+        sgd_update_kernel<<<grid, 256, 0, st>>>(X, ldx, M, ldm, ws.G, ws.ldg, task_row, task_peer,
+                                                s == 0 ? mom_first : nullptr, p.gcount, gnl::P, lr, mu, wd);
+        DLS_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G, int64_t ldg,
+                             const int32_t *task_row, const uint8_t *images, const int64_t *labels,
+                             const int32_t *mb_index, const int32_t *mb_count, int32_t n_tasks,
+                             int32_t batch, float *loss_out, int32_t precision, void *workspace,
+                             int64_t workspace_bytes, void *stream)
+{
+    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (precision != 0) return DLS_E_SHAPE;
+    if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0)
+        return DLS_E_ARG;
+    if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
+    int rc = check_rows(X, ldx, gnl::P);
+    if (rc) return rc;
+    if ((rc = check_rows(G, ldg, gnl::P))) return rc;
+    if (n_tasks == 0) return 0;
+    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, false)) return DLS_E_WS;
+    gnl::Workspace ws;
+    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, false);
+    ws.G = G; ws.ldg = ldg;
+    gnl::Pass p;
+    p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks;
+    p.gmodel = nullptr; p.mrow = task_row; p.img_idx = mb_index; p.gcount = mb_count;
+    p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
+    return gnl_step(p, ws, loss_out, (cudaStream_t)stream);
+}
+
+extern "C" int64_t dls_eval_workspace_bytes(int32_t arch, int32_t n_models, int32_t n_test)
+{
+    if (arch != DLS_ARCH_GNLENET || n_models < 0 || n_test < 0) return DLS_E_SHAPE;
+    const int gpm = (n_test + EVAL_GS - 1) / EVAL_GS;
+    const int64_t total_groups = (int64_t)n_models * gpm;
+    const int chunk = (int)(total_groups < EVAL_CHUNK_GROUPS ? total_groups : EVAL_CHUNK_GROUPS);
+    return gnl::workspace_bytes(chunk > 0 ? chunk : 1, EVAL_GS, n_models, false, false) +
+           total_groups * 2 * (int64_t)sizeof(float) + 1024;
+}
+
+extern "C" int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const int32_t *model_rows,
+                             int32_t n_models, const uint8_t *test_images, const int64_t *test_labels,
+                             int32_t n_test, int32_t *out_correct, double *out_loss_sum,
+                             float *out_logits, int32_t precision, void *workspace,
+                             int64_t workspace_bytes, void *stream)
+{
+    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (precision != 0) return DLS_E_SHAPE;
+    if (!model_rows || !test_images || !test_labels || !out_correct || !out_loss_sum || !workspace ||
+        n_models < 0 || n_test < 0)
+        return DLS_E_ARG;
+    int rc = check_rows(X, ldx, gnl::P);
+    if (rc) return rc;
+    if (n_models == 0 || n_test == 0) return 0;
+    if (workspace_bytes < dls_eval_workspace_bytes(arch, n_models, n_test)) return DLS_E_WS;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int gpm = (n_test + EVAL_GS - 1) / EVAL_GS;
+    const int64_t total_groups = (int64_t)n_models * gpm;
+    const int chunk = (int)(total_groups < EVAL_CHUNK_GROUPS ? total_groups : EVAL_CHUNK_GROUPS);
+    gnl::Workspace ws;
+    const int64_t used = gnl::carve(ws, workspace, chunk, EVAL_GS, n_models, false, false);
+    float *glog_all = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + used);
+    int32_t *d_img_idx = ws.desc_i32;
+    int32_t *d_gmodel = ws.desc_i32 + (int64_t)chunk * EVAL_GS;
+    int32_t *d_gcount = d_gmodel + chunk;
+    gnl::Pass p;
+    p.gs = EVAL_GS; p.n_models = n_models; p.gmodel = d_gmodel; p.mrow = model_rows;
+    p.img_idx = d_img_idx; p.gcount = d_gcount; p.images = test_images; p.labels = test_labels;
+    p.X = X; p.ldx = ldx; p.n_groups = chunk;
+    if ((rc = gnl::prep_weights(p, ws, false, st))) return rc;
+    for (int64_t g0 = 0; g0 < total_groups; g0 += chunk) {
+        const int ng = (int)((total_groups - g0) < chunk ? (total_groups - g0) : chunk);
+        p.n_groups = ng;
+        eval_desc_kernel<<<(ng * EVAL_GS + 255) / 256, 256, 0, st>>>(d_gmodel, d_img_idx, d_gcount, (int)g0, ng,
+                                                                      EVAL_GS, gpm, n_test);
+        DLS_LAUNCH_CHECK();
+        ws.glog = glog_all + g0 * 2;
+        if ((rc = gnl::forward(p, ws, false, st))) return rc;
+        if ((rc = gnl::classifier(p, ws, 1, nullptr, out_logits, n_test * gnl::NCLS, st))) return rc;
+    }
+    eval_reduce_kernel<<<(n_models + 127) / 128, 128, 0, st>>>(glog_all, gpm, n_models, out_correct, out_loss_sum);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}

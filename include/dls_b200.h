@@ -1,0 +1,128 @@
+/*
+ * dls_b200 — C-ABI of the B200 (sm_100a) batched executor for the decentralized-learning
+ * simulator's compute-graph solve (train / aggregate / test tasks).
+ *
+ * Boundary: the reference runs one task of one simulated node per call through
+ *   Worker.start                      dasklearn/worker.py:21-38
+ *   functions.train/aggregate/test    dasklearn/functions.py:28-77, 89-106, 109-133
+ * This library executes a whole wavefront of same-kind tasks per call on rows of the stacked
+ * parameter tensor `[S, ld]` (one fp32 row per node model, `parameters()` order).
+ *
+ * Conventions
+ *   - plain C symbols, raw DEVICE pointers, explicit cudaStream_t (passed as void*);
+ *   - the caller owns every buffer including workspaces; calls are asynchronous on `stream`;
+ *   - return value: 0 = ok, negative = argument/shape error (DLS_E_*), positive = cudaError_t;
+ *   - no CPU fallback: without a CUDA device every compute entry point returns an error.
+ *   - rows must be 16-byte aligned: `ld % 4 == 0` and 16-byte aligned base pointers.
+ */
+#ifndef DLS_B200_H
+#define DLS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLS_E_ARG      (-1)   /* null pointer / negative size */
+#define DLS_E_ALIGN    (-2)   /* pointer or leading dimension not 16-byte aligned */
+#define DLS_E_SHAPE    (-3)   /* unsupported shape (batch too large, ld < P, ...) */
+#define DLS_E_WS       (-4)   /* workspace too small */
+#define DLS_E_TOO_BIG  (-5)   /* request exceeds a compiled-in maximum */
+
+/* Model families (dasklearn/models/__init__.py:19-42): 0 = GNLeNet (cifar10), 1 = FEMNIST CNN */
+#define DLS_ARCH_GNLENET 0
+#define DLS_ARCH_FEMNIST 1
+
+#define DLS_GNLENET_P   85354
+#define DLS_FEMNIST_P 1690046
+#define DLS_MAX_GROUP      64   /* max minibatch size (settings.learning.batch_size) */
+
+/* Library / build information. */
+int         dls_version(void);
+const char *dls_build_info(void);
+/* Number of kernels this library has launched in the calling process (all entry points). */
+int64_t     dls_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * aggregate wave — replaces N calls of functions.aggregate -> ModelManager ->
+ * FedAvg.aggregate (dasklearn/functions.py:89-106, dasklearn/model_manager.py:27-43,
+ * dasklearn/gradient_aggregation/fedavg.py:12-26).
+ *
+ *   Y[out_rows[r], 0:P] = sum_{e in [rowptr[r], rowptr[r+1])} wval[e] * X[src_rows[colidx[e]], 0:P]
+ *
+ * evaluated per element in list order as acc = x_first*0; acc = fadd_rn(acc, fmul_rn(w, x))
+ * (separate multiply and add, no FMA) — bit-identical to the reference's
+ * `center.add_(w * p)` loop.  `src_rows` lists the n_src_rows distinct source rows of the wave
+ * (NULL = identity: colidx indexes X directly); `out_rows == NULL` means row r.  X and Y may be
+ * the same allocation as long as no output row is also an input row of the same call.
+ * `variant`: 0 = auto, 1 = gather through L2, 2 = shared-memory staged column tiles.
+ * ------------------------------------------------------------------------------------------ */
+int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t ldy,
+                     const int32_t *rowptr, const int32_t *colidx, const float *wval,
+                     const int32_t *src_rows, const int32_t *out_rows, int32_t n_rows,
+                     int32_t n_src_rows, int64_t P, int32_t variant, void *stream);
+
+/* Row plumbing on the stacked tensor (replaces the pickle round-trip copies of
+ * serialize_model/unserialize_model, dasklearn/models/__init__.py:9-16). */
+int dls_copy_rows(const float *X, int64_t ldx, float *Y, int64_t ldy, const int32_t *src_rows,
+                  const int32_t *dst_rows, int32_t n_rows, int64_t P, void *stream);
+int dls_broadcast_row(const float *src, float *Y, int64_t ldy, const int32_t *dst_rows,
+                      int32_t n_rows, int64_t P, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * train wave — replaces N calls of functions.train -> ModelTrainer.train
+ * (dasklearn/functions.py:28-77, dasklearn/model_trainer.py:60-131) + torch.optim.SGD
+ * (dasklearn/optimizer/sgd.py:4-14).
+ *
+ * One call runs up to `n_steps` local SGD steps for `n_tasks` nodes, in place on their rows.
+ *   X, ldx        stacked parameters; task t trains row task_row[t]
+ *   M, ldm        momentum buffers, one row per NODE; task t uses row task_peer[t]
+ *                 (momentum persists per node across rounds, model_trainer.py:89-92);
+ *                 may be NULL when mu == 0
+ *   mom_first[t]  1 if node task_peer[t] has no momentum buffer yet (buf = grad on its first step)
+ *   images/labels the nodes' uint8 HWC partitions, image i at images + i*img_bytes
+ *   mb_index      [n_steps][n_tasks][batch] GLOBAL image ids (-1 = empty slot)
+ *   mb_count      [n_steps][n_tasks] delivered batch size (0 = task already finished its loader)
+ *   loss_out      optional [n_steps][n_tasks] mean minibatch loss
+ * Loss: NLL of log_softmax (GNLeNet) / cross entropy (FEMNIST), mean over the delivered batch.
+ * Math: fp32 CUDA-core kernels when `precision == 0`; `precision == 1` uses bf16 tensor-core
+ * operands with fp32 accumulation for the convolution GEMMs.
+ * ------------------------------------------------------------------------------------------ */
+int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int32_t batch);
+int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int64_t ldm,
+                   const int32_t *task_row, const int32_t *task_peer, const uint8_t *mom_first,
+                   const uint8_t *images, const int64_t *labels,
+                   const int32_t *mb_index, const int32_t *mb_count,
+                   int32_t n_tasks, int32_t n_steps, int32_t batch,
+                   float lr, float mu, float wd, float *loss_out, int32_t precision,
+                   void *workspace, int64_t workspace_bytes, void *stream);
+
+/* Gradient of one minibatch per task, written to G[t, 0:P] (no update).  Exposes the backward
+ * pass for compute_gradient tasks (dasklearn/functions.py:80-82) and for parity tests. */
+int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G, int64_t ldg,
+                  const int32_t *task_row, const uint8_t *images, const int64_t *labels,
+                  const int32_t *mb_index, const int32_t *mb_count, int32_t n_tasks, int32_t batch,
+                  float *loss_out, int32_t precision, void *workspace, int64_t workspace_bytes,
+                  void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * test wave — replaces N calls of functions.test -> ModelEvaluator.evaluate_accuracy
+ * (dasklearn/functions.py:109-133, dasklearn/model_evaluator.py:26-64).
+ *
+ * Evaluates `n_models` rows on the same `n_test` images.  Outputs per model:
+ *   out_correct[m]   number of argmax hits (first maximum wins, like torch.argmax)
+ *   out_loss_sum[m]  sum over samples of the per-sample loss (fp64 accumulation of fp32 terms)
+ * The caller derives accuracy = correct / n_test * 100 and loss = loss_sum / n_test.
+ * ------------------------------------------------------------------------------------------ */
+int64_t dls_eval_workspace_bytes(int32_t arch, int32_t n_models, int32_t n_test);
+int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const int32_t *model_rows,
+                  int32_t n_models, const uint8_t *test_images, const int64_t *test_labels,
+                  int32_t n_test, int32_t *out_correct, double *out_loss_sum,
+                  float *out_logits /* optional [n_models][n_test][classes] */, int32_t precision,
+                  void *workspace, int64_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLS_B200_H */

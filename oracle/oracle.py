@@ -188,7 +188,7 @@ def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarr
     out = forward(layout, wl, to_tensor(images_u8))
     loss = loss_fn(layout, out, torch.from_numpy(labels.astype(np.int64)))
     loss.backward()
-    return wl.grad.numpy().copy(), float(loss)
+    return wl.grad.numpy().copy(), float(loss.detach())
 
 
 # ---------------------------------------------------------------------------------------------

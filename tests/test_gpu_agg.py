@@ -1,0 +1,141 @@
+"""Aggregate wave (CUDA, through the C-ABI) against the oracle: bit-exact."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+import dls_b200
+from dls_b200 import kernels as K, synthetic
+from dls_b200.layout import GNLENET as L
+from katgen import kat_rows
+
+pytestmark = pytest.mark.gpu
+
+
+def _csr(models_lists, weights_lists=None):
+    rowptr = [0]
+    col, w = [], []
+    for i, ms in enumerate(models_lists):
+        ws = weights_lists[i] if weights_lists else [float(1.0 / len(ms))] * len(ms)
+        col += list(ms)
+        w += [np.float32(x) for x in ws]
+        rowptr.append(len(col))
+    return (np.array(rowptr, np.int32), np.array(col, np.int32), np.array(w, np.float32))
+
+
+def _run(cuda, X, rowptr, col, w, P, variant, src_rows=None, out_rows=None, n_out=None):
+    Xd = torch.from_numpy(X).to(cuda)
+    n_out = n_out or (len(rowptr) - 1)
+    Yd = torch.full((n_out, X.shape[1]), float("nan"), device=cuda)
+    K.agg_spmm(Xd, Yd, torch.from_numpy(rowptr).to(cuda), torch.from_numpy(col).to(cuda),
+               torch.from_numpy(w).to(cuda), P,
+               src_rows=None if src_rows is None else torch.from_numpy(src_rows).to(cuda),
+               out_rows=None if out_rows is None else torch.from_numpy(out_rows).to(cuda), variant=variant)
+    torch.cuda.synchronize()
+    return Yd.cpu().numpy()
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("tag,fan,weighted", [("f5", 5, False), ("f11", 11, False), ("f2w", 2, True), ("f5w", 5, True)])
+def test_golden_fedavg(cuda, golden_dir, variant, tag, fan, weighted):
+    """Same inputs as the reference-generated fixture: CUDA result == reference bits."""
+    g = np.load(os.path.join(golden_dir, "fedavg_kat.npz"))
+    X = np.zeros((fan, L.ld), np.float32)
+    X[:, :L.P] = kat_rows(fan, L.P, salt=fan + (100 if weighted else 0))
+    ws = [list(g[tag + "_w"])] if weighted else None
+    rowptr, col, w = _csr([list(range(fan))], ws)
+    Y = _run(cuda, X, rowptr, col, w, L.P, variant)
+    assert np.array_equal(Y[0, :L.P].view(np.uint32), g[tag + "_y"].view(np.uint32))
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("n,k", [(16, 4), (64, 6), (200, 7)])
+def test_wave_vs_oracle(cuda, variant, n, k):
+    """A whole D-PSGD aggregate wave on a k-regular topology, shuffled arrival order, own model last."""
+    if (n * k) % 2:
+        k += 1
+    nb = synthetic.kreg_topology(n, k, seed=42)
+    rs = np.random.RandomState(n)
+    lists = []
+    for i in range(n):
+        l = list(nb[i])
+        rs.shuffle(l)
+        lists.append(l + [i])
+    rowptr, col, w = _csr(lists)
+    X = np.zeros((n, L.ld), np.float32)
+    X[:, :L.P] = kat_rows(n, L.P, salt=n)
+    Y = _run(cuda, X, rowptr, col, w, L.P, variant)
+    Yo = O.fedavg_csr(X, rowptr, col, w, L.P)
+    assert np.array_equal(Y[:, :L.P].view(np.uint32), Yo[:, :L.P].view(np.uint32))
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_ragged_rows_slots_and_special_values(cuda, variant):
+    """Variable fan-in (churn), explicit weights, indirection through src_rows/out_rows, fan-in 1,
+    fan-in > 64 (multiple staging passes), -0.0 / inf / nan propagation, P not a multiple of 4."""
+    P, ld = 1001, 1024
+    n_src = 70
+    rs = np.random.RandomState(3)
+    pool = np.zeros((100, ld), np.float32)
+    pool[:, :P] = rs.standard_normal((100, P)).astype(np.float32)
+    pool[7, :8] = [-0.0, np.inf, -np.inf, np.nan, 0.0, 1e-45, -1e38, 3e38]
+    pool[9, :8] = [-0.0, 1.0, np.inf, 1.0, -0.0, 1e-45, -3e38, 3e38]
+    src_rows = rs.permutation(100)[:n_src].astype(np.int32)
+    src_rows[0], src_rows[1] = 7, 9
+    lists = [[0], [0, 1], [1, 0, 5], list(range(n_src)), [3, 3, 3], list(rs.permutation(n_src)[:9])]
+    weights = [[1.0], [0.5, 0.5], [0.2, 0.3, 0.5], [1.0 / n_src] * n_src, [0.1, 0.2, 0.7],
+               list(rs.rand(9).astype(np.float64))]
+    rowptr, col, w = _csr(lists, weights)
+    out_rows = np.array([5, 0, 3, 1, 4, 2], np.int32)
+    Y = _run(cuda, pool, rowptr, col, w, P, variant, src_rows=src_rows, out_rows=out_rows, n_out=6)
+    Xs = pool[src_rows]
+    Yo = O.fedavg_csr(Xs, rowptr, col, w, P, out_rows=out_rows, n_out=6)
+    # NaN payload/sign bits are not defined by IEEE-754 arithmetic (x86 and the GPU pick different
+    # canonical NaNs): NaNs must be in the same places, every other value bit-identical (incl. -0.0)
+    nan_g, nan_o = np.isnan(Y[:, :P]), np.isnan(Yo[:, :P])
+    assert np.array_equal(nan_g, nan_o) and nan_o.sum() >= 4
+    assert np.array_equal(Y[:, :P].view(np.uint32)[~nan_o], Yo[:, :P].view(np.uint32)[~nan_o])
+
+
+def test_empty_wave_and_unaligned_rows(cuda):
+    X = torch.zeros((4, 64), device=cuda)
+    Y = torch.zeros((4, 64), device=cuda)
+    rp = torch.zeros(1, dtype=torch.int32, device=cuda)
+    K.agg_spmm(X, Y, rp, rp, torch.zeros(1, device=cuda), 64)      # zero rows: no-op
+    # unaligned leading dimension -> scalar path, still bit-exact
+    P, ld = 37, 39
+    rs = np.random.RandomState(0)
+    Xn = rs.standard_normal((6, ld)).astype(np.float32)
+    rowptr, col, w = _csr([[1, 2, 0], [5, 4]])
+    Yd = _run(cuda, Xn, rowptr, col, w, P, 1)
+    Yo = O.fedavg_csr(Xn, rowptr, col, w, P)
+    assert np.array_equal(Yd[:2, :P].view(np.uint32), Yo[:, :P].view(np.uint32))
+
+
+def test_linearity_and_fixed_point_full_size(cuda):
+    """Size-independent properties at the full C2 size (256 nodes x GNLeNet): a wave over
+    identical rows returns that row (up to the reference's rounding), and a permutation
+    matrix reproduces the input bits."""
+    n = 256
+    Xd = torch.randn((n, L.ld), device=cuda)
+    perm = torch.randperm(n, device=cuda).to(torch.int32)
+    rowptr = torch.arange(n + 1, dtype=torch.int32, device=cuda)
+    Y = torch.empty_like(Xd)
+    K.agg_spmm(Xd, Y, rowptr, perm, torch.ones(n, device=cuda), L.P, variant=1)
+    assert torch.equal(Y[:, :L.P], Xd[perm.long(), :L.P])
+    Y2 = torch.empty_like(Xd)
+    K.agg_spmm(Xd, Y2, rowptr, perm, torch.ones(n, device=cuda), L.P, variant=2)
+    assert torch.equal(Y2[:, :L.P], Y[:, :L.P])
+
+
+def test_copy_and_broadcast_rows(cuda):
+    X = torch.randn((8, L.ld), device=cuda)
+    Y = torch.zeros((8, L.ld), device=cuda)
+    src = torch.tensor([3, 1], dtype=torch.int32, device=cuda)
+    dst = torch.tensor([0, 7], dtype=torch.int32, device=cuda)
+    K.copy_rows(X, Y, src, dst, L.P)
+    assert torch.equal(Y[0, :L.P], X[3, :L.P]) and torch.equal(Y[7, :L.P], X[1, :L.P])
+    K.broadcast_row(X[5], Y, torch.arange(8, dtype=torch.int32, device=cuda), L.P)
+    assert torch.equal(Y[:, :L.P], X[5, :L.P].expand(8, L.P))

@@ -1,0 +1,211 @@
+"""Wave executor: the stacked parameter tensor in HBM plus batched train / aggregate / test.
+
+Replaces the per-node learning core the reference worker calls one task at a time
+(`ModelTrainer` dasklearn/model_trainer.py, `ModelManager`/`FedAvg`
+dasklearn/model_manager.py + gradient_aggregation/fedavg.py, `ModelEvaluator`
+dasklearn/model_evaluator.py).  State that the reference keeps in process globals
+(`model_trainers[peer].optimizer`, dasklearn/functions.py:22-25,50-51) lives here as the momentum
+matrix `M[node]` and the `mom_valid[node]` flags.
+"""
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import kernels as K
+from ._lib import DlsError
+from .dataset import DeviceDataset
+from .layout import ModelLayout, layout_for
+from .models import initial_row
+from .util import MICROSECONDS
+
+
+class RowHandle:
+    """Opaque result of a task: one row (slot) of the executor's stacked tensor.  This is what
+    the API-compatible `train/aggregate/test` functions return in place of an `nn.Module`."""
+    __slots__ = ("executor", "slot")
+
+    def __init__(self, executor: "WaveExecutor", slot: int):
+        self.executor = executor
+        self.slot = slot
+
+    def numpy(self) -> np.ndarray:
+        return self.executor.X[self.slot, :self.executor.layout.P].cpu().numpy()
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        from .layout import unflatten_row
+        return unflatten_row(self.executor.layout, self.executor.X[self.slot].cpu())
+
+    def __repr__(self):
+        return "<RowHandle slot=%d>" % self.slot
+
+
+class WaveExecutor:
+    def __init__(self, settings, dataset: DeviceDataset, device=None, n_slots: Optional[int] = None,
+                 node_ids: Optional[Sequence[int]] = None):
+        if not torch.cuda.is_available():
+            raise DlsError("the B200 executor needs a CUDA device (there is no CPU fallback)")
+        self.settings = settings
+        self.layout: ModelLayout = layout_for(settings.dataset, settings.model)
+        self.device = device or torch.device(settings.torch_device_name if "cuda" in str(settings.torch_device_name)
+                                             else "cuda:0")
+        self.dataset = dataset
+        self.precision = int(getattr(settings, "precision", 0))
+        # nodes this executor owns (multi-GPU: a contiguous block per rank)
+        ids = list(node_ids) if node_ids is not None else list(range(settings.participants))
+        self.node_ids = ids
+        self.local_of = {int(n): i for i, n in enumerate(ids)}
+        n_local = len(ids)
+        self.n_slots = n_slots or (2 * n_local + 2)
+        ld = self.layout.ld
+        self.X = torch.zeros((self.n_slots, ld), dtype=torch.float32, device=self.device)
+        self.free: List[int] = list(range(self.n_slots - 1, -1, -1))
+        self.refs = np.zeros(self.n_slots, dtype=np.int64)
+        mu = float(settings.learning.momentum)
+        self.M = torch.zeros((n_local, ld), dtype=torch.float32, device=self.device) if mu != 0 else None
+        self.mom_valid = np.zeros(n_local, dtype=bool)
+        self.init_row = initial_row(self.layout, settings.seed).to(self.device)
+        self.ws = K.Workspace(self.device)
+        self.stats = {"train_tasks": 0, "train_steps": 0, "agg_rows": 0, "test_tasks": 0}
+
+    # -- slot pool --------------------------------------------------------------------------
+    def alloc(self, n: int = 1) -> List[int]:
+        if len(self.free) < n:
+            self._grow(max(n - len(self.free), self.n_slots // 2))
+        return [self.free.pop() for _ in range(n)]
+
+    def _grow(self, extra: int):
+        X2 = torch.zeros((self.n_slots + extra, self.layout.ld), dtype=torch.float32, device=self.device)
+        X2[:self.n_slots].copy_(self.X)
+        self.X = X2
+        self.refs = np.concatenate([self.refs, np.zeros(extra, dtype=np.int64)])
+        self.free = list(range(self.n_slots + extra - 1, self.n_slots - 1, -1)) + self.free
+        self.n_slots += extra
+
+    def retain(self, slot: int, n: int = 1):
+        self.refs[slot] += n
+
+    def release(self, slot: int, n: int = 1):
+        self.refs[slot] -= n
+        assert self.refs[slot] >= 0
+        if self.refs[slot] == 0:
+            self.free.append(slot)
+
+    def _dev_i32(self, a) -> torch.Tensor:
+        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.int32)).to(self.device, non_blocking=True)
+
+    # -- waves ------------------------------------------------------------------------------
+    def init_rows(self, slots: Sequence[int]):
+        """Identical initial model for every node (dasklearn/functions.py:46-48)."""
+        if len(slots):
+            K.broadcast_row(self.init_row, self.X, self._dev_i32(slots), self.layout.P)
+
+    def copy_rows(self, src: Sequence[int], dst: Sequence[int]):
+        if len(src):
+            K.copy_rows(self.X, self.X, self._dev_i32(src), self._dev_i32(dst), self.layout.P)
+
+    def train_wave(self, slots: Sequence[int], peers: Sequence[int], rounds: Sequence[int],
+                   steps: Optional[Sequence[int]] = None, prepared=None, loss_out=None):
+        """In-place local SGD on `slots` for nodes `peers` (functions.train for every task)."""
+        ls = self.settings.learning
+        T = len(slots)
+        if T == 0:
+            return
+        if prepared is None:
+            prepared = self.prepare_train(peers, rounds, steps)
+        mb_index, mb_count, n_steps_done = prepared
+        local = [self.local_of[int(p)] for p in peers]
+        if len(set(local)) != len(local):
+            raise DlsError("a train wave holds two tasks of the same node; they must run in different waves")
+        first = np.array([0 if self.mom_valid[l] else 1 for l in local], dtype=np.uint8)
+        K.train_wave(self.layout, self.X, self.M, self._dev_i32(slots), self._dev_i32(local),
+                     torch.from_numpy(first).to(self.device, non_blocking=True), self.dataset.images,
+                     self.dataset.labels, mb_index, mb_count, int(ls.batch_size), float(ls.learning_rate),
+                     float(ls.momentum), float(ls.weight_decay), self.ws, loss_out=loss_out,
+                     precision=self.precision)
+        if self.M is not None:
+            for l, n in zip(local, n_steps_done):
+                if n > 0:
+                    self.mom_valid[l] = True
+        self.stats["train_tasks"] += T
+        self.stats["train_steps"] += int(sum(n_steps_done))
+
+    def prepare_train(self, peers, rounds, steps=None):
+        """Host->device staging of a train wave's minibatch index (the analogue of the DataLoader)."""
+        ls = self.settings.learning
+        steps = list(steps) if steps is not None else [int(ls.local_steps)] * len(peers)
+        idx, cnt = self.dataset.minibatches(peers, rounds, int(ls.batch_size), steps)
+        done = (cnt > 0).sum(axis=0).tolist()
+        pin = torch.cuda.is_available()
+        ti = torch.from_numpy(idx)
+        tc = torch.from_numpy(cnt)
+        if pin:
+            ti, tc = ti.pin_memory(), tc.pin_memory()
+        return ti.to(self.device, non_blocking=True), tc.to(self.device, non_blocking=True), done
+
+    def aggregate_wave(self, model_slots: Sequence[Sequence[int]], out_slots: Sequence[int],
+                       weights: Optional[Sequence[Optional[Sequence[float]]]] = None, variant: int = 0,
+                       prepared=None):
+        """FedAvg for every task of the wave: `model_slots[r]` is task r's `models` list as slots
+        in list order (dasklearn/gradient_aggregation/fedavg.py:12-26)."""
+        if len(out_slots) == 0:
+            return
+        if prepared is None:
+            prepared = self.prepare_aggregate(model_slots, out_slots, weights)
+        rowptr, colidx, wval, src_rows, out_rows, n_src = prepared
+        K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows, out_rows=out_rows,
+                   n_src_rows=n_src, variant=variant)
+        self.stats["agg_rows"] += len(out_slots)
+
+    def prepare_aggregate(self, model_slots, out_slots, weights=None):
+        rowptr = np.zeros(len(out_slots) + 1, dtype=np.int32)
+        src_index: Dict[int, int] = {}
+        col: List[int] = []
+        w: List[float] = []
+        for r, ms in enumerate(model_slots):
+            ws = weights[r] if (weights is not None and weights[r]) else None
+            if ws is None:
+                ws = [float(1.0 / len(ms))] * len(ms)            # fedavg.py:14-15
+            elif len(ws) != len(ms):
+                raise AssertionError("len(weights) != len(models)")   # fedavg.py:17
+            for s, wt in zip(ms, ws):
+                col.append(src_index.setdefault(int(s), len(src_index)))
+                w.append(wt)
+            rowptr[r + 1] = len(col)
+        src_rows = np.fromiter(src_index.keys(), dtype=np.int32, count=len(src_index))
+        if set(src_index) & set(int(o) for o in out_slots):
+            raise DlsError("aggregate wave would overwrite one of its own inputs")
+        dev = self.device
+        return (torch.from_numpy(rowptr).to(dev, non_blocking=True),
+                torch.from_numpy(np.asarray(col, dtype=np.int32)).to(dev, non_blocking=True),
+                torch.from_numpy(np.asarray(w, dtype=np.float64).astype(np.float32)).to(dev, non_blocking=True),
+                torch.from_numpy(src_rows).to(dev, non_blocking=True),
+                self._dev_i32(out_slots), len(src_index))
+
+    def test_wave(self, slots: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
+        """(accuracy %, mean loss) per slot on the whole test split
+        (ModelEvaluator.evaluate_accuracy, dasklearn/model_evaluator.py:26-64)."""
+        if len(slots) == 0:
+            return np.zeros(0), np.zeros(0)
+        correct, loss = K.eval_wave(self.layout, self.X, self._dev_i32(slots), self.dataset.test_images,
+                                    self.dataset.test_labels, self.ws, precision=self.precision)
+        n = float(self.dataset.test_labels.numel())
+        acc = correct.cpu().numpy().astype(np.float64) / n * 100.0
+        ls = loss.cpu().numpy() / n
+        self.stats["test_tasks"] += len(slots)
+        return acc, ls
+
+    # -- accuracy CSV, same rows as dasklearn/functions.py:121-128 --------------------------------
+    def write_accuracy(self, peer: int, round_nr: int, cur_time: int, accuracy: float, loss: float):
+        s = self.settings
+        data_dir = getattr(s, "data_dir", "") or "."
+        os.makedirs(data_dir, exist_ok=True)
+        path = os.path.join(data_dir, "accuracies_" + str(peer) + ".csv")
+        if not os.path.exists(path):
+            with open(path, "w") as f:
+                f.write("algorithm,dataset,partitioner,alpha,peer,round,time,accuracy,loss\n")
+        with open(path, "a") as f:
+            f.write("%s,%s,%s,%g,%d,%d,%.2f,%f,%f\n" % (
+                s.algorithm, s.dataset, getattr(s, "partitioner", "iid"), getattr(s, "alpha", 1), peer, round_nr,
+                cur_time / MICROSECONDS, accuracy, loss))

@@ -1,0 +1,91 @@
+"""API-compatible task entry points: `train`, `aggregate`, `test` with the signature
+`f(settings, params) -> [result]` of the reference (dasklearn/functions.py:28-77, 89-106,
+109-133), looked up by name by the worker loop (`globals()[func_name]`, dasklearn/worker.py:27-31).
+
+Differences that the DAG format hides: results are opaque `RowHandle`s (rows of the stacked
+HBM tensor) instead of `nn.Module`s, and the dataset is a device-resident `DeviceDataset`
+(set with `set_dataset`, the analogue of the module-global `dataset` of functions.py:23,40-41).
+A single call is simply a wave of one task; the batched solver (`solver.BatchedSolver`) is the
+fast path."""
+import logging
+import threading
+from typing import Dict, List, Optional
+
+from ._lib import DlsError
+from .dataset import DeviceDataset
+from .executor import RowHandle, WaveExecutor
+
+logger = logging.getLogger(__name__)
+executor: Optional[WaveExecutor] = None      # process-global like `model_trainers` (functions.py:22)
+dataset: Optional[DeviceDataset] = None      # process-global like `dataset`        (functions.py:23)
+lock = threading.Lock()
+
+
+def set_dataset(ds: Optional[DeviceDataset]):
+    global dataset, executor
+    dataset = ds
+    executor = None
+
+
+def get_executor(settings) -> WaveExecutor:
+    global executor
+    with lock:
+        if executor is None:
+            if dataset is None:
+                raise DlsError("no dataset: call dls_b200.functions.set_dataset(DeviceDataset...) first")
+            executor = WaveExecutor(settings, dataset)
+    return executor
+
+
+def _slot_of(model, ex: WaveExecutor) -> int:
+    if not isinstance(model, RowHandle) or model.executor is not ex:
+        raise DlsError("model is not a RowHandle of this executor: %r" % (model,))
+    return model.slot
+
+
+def train(settings, params: Dict) -> List[RowHandle]:
+    model = params["model"]
+    if isinstance(model, tuple):        # first round: the tuple (None, 0)  (functions.py:30-32)
+        model = model[0]
+    peer_id = params["peer"]
+    if params.get("compute_gradient") or params.get("gradient_model") is not None:
+        raise DlsError("compute_gradient / gradient_update tasks are not implemented by this executor")
+    local_steps = params["local_steps"] if "local_steps" in params else settings.learning.local_steps
+    ex = get_executor(settings)
+    out = ex.alloc(1)[0]
+    ex.retain(out)
+    if not model:
+        ex.init_rows([out])             # torch.manual_seed(seed); create_model(...)  (functions.py:46-48)
+    else:
+        ex.copy_rows([_slot_of(model, ex)], [out])   # the result is a detached copy (functions.py:64-70)
+    ex.train_wave([out], [peer_id], [params["round"]], [local_steps])
+    return [RowHandle(ex, out)]
+
+
+def aggregate(settings, params: Dict) -> List[RowHandle]:
+    models = params["models"]
+    weights = params["weights"] if "weights" in params else None
+    ex = get_executor(settings)
+    out = ex.alloc(1)[0]
+    ex.retain(out)
+    ex.aggregate_wave([[_slot_of(m, ex) for m in models]], [out], [weights])
+    return [RowHandle(ex, out)]
+
+
+def test(settings, params: Dict) -> List[RowHandle]:
+    model = params["model"]
+    ex = get_executor(settings)
+    slot = _slot_of(model, ex)
+    acc, loss = ex.test_wave([slot])
+    ex.write_accuracy(params["peer"], params["round"], params["time"], float(acc[0]), float(loss[0]))
+    logger.info("[t=%.2f] Model accuracy (peer %d, round %d): %f, loss: %f", params["time"] / 1e6,
+                params["peer"], params["round"], acc[0], loss[0])
+    out = ex.alloc(1)[0]                # the reference returns a copy of the model (functions.py:132)
+    ex.retain(out)
+    ex.copy_rows([slot], [out])
+    return [RowHandle(ex, out)]
+
+
+def release(handle: RowHandle):
+    """Give a row back to the pool (the reference relies on Python GC of nn.Modules)."""
+    handle.executor.release(handle.slot)

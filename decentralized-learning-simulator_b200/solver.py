@@ -1,0 +1,279 @@
+"""Batched compute-graph solver: the drop-in replacement for the broker's ready-queue loop +
+worker processes (`Broker.handle_task_result` dasklearn/broker.py:277-290, `Worker.start`
+dasklearn/worker.py:21-38).
+
+Input is exactly what a broker receives in the coordinator's `config` message: the serialized
+task list (`WorkflowDAG.serialize()`, dasklearn/tasks/dag.py:28-32; task dict format
+dasklearn/tasks/task.py:59-66).  Instead of dispatching one ready task at a time, the solver
+levelises the DAG into wavefronts, groups every wavefront by task function and runs each group
+as ONE batched GPU wave on rows of the stacked parameter tensor.
+
+`plan()` does all host-side work once (levelisation, slot assignment with reference counts,
+CSR construction, minibatch index); `run()` then only uploads per-wave descriptors and launches.
+"""
+from collections import defaultdict
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ._lib import DlsError
+from .executor import RowHandle, WaveExecutor
+
+TRAIN_FUNCS = ("train",)
+SUPPORTED = ("train", "aggregate", "test")
+
+
+class Wave:
+    __slots__ = ("level", "func", "names", "peers", "rounds", "times", "steps", "in_slots", "out_slots",
+                 "model_slots", "weights", "init_slots", "copy_src", "copy_dst", "release_after", "prepared")
+
+    def __init__(self, level: int, func: str):
+        self.level, self.func = level, func
+        self.names: List[str] = []
+        self.peers: List[int] = []
+        self.rounds: List[int] = []
+        self.times: List[int] = []
+        self.steps: List[int] = []
+        self.in_slots: List[int] = []
+        self.out_slots: List[int] = []
+        self.model_slots: List[List[int]] = []
+        self.weights: List[Optional[List[float]]] = []
+        self.init_slots: List[int] = []
+        self.copy_src: List[int] = []
+        self.copy_dst: List[int] = []
+        self.release_after: List[int] = []
+        self.prepared = None
+
+
+class BatchedSolver:
+    def __init__(self, executor: WaveExecutor, serialized_tasks: Sequence[Dict],
+                 on_sink: Optional[Callable[[str, List[RowHandle]], None]] = None,
+                 owned_peers: Optional[Sequence[int]] = None, agg_variant: int = 0):
+        self.ex = executor
+        self.tasks: Dict[str, Dict] = {}
+        for t in serialized_tasks:
+            if t["func"] not in SUPPORTED:
+                # same failure mode as the worker: unknown function name (dasklearn/worker.py:26-27)
+                raise RuntimeError("Task function %s not found!" % t["func"])
+            self.tasks[t["name"]] = t
+        self.on_sink = on_sink
+        self.agg_variant = agg_variant
+        self.owned = set(int(p) for p in owned_peers) if owned_peers is not None else None
+        self.waves: List[Wave] = []
+        self.sink_slots: Dict[str, int] = {}
+        self.wave_times: List[Tuple[str, int, float]] = []   # (func, n_tasks, ms) when timing is on
+        self.planned = False
+        self.initial_models: Dict[int, int] = {}              # peer -> slot holding its current model
+        self.h2d_bytes = 0
+        self.last_train_loss = None
+
+    def seed_models(self, slots_by_peer: Dict[int, int]):
+        """Continue from models already in HBM: a `train` task whose model is `(None, 0)` starts
+        from `slots_by_peer[peer]` instead of the initial model (used to solve a long run one
+        round-graph at a time)."""
+        self.initial_models = dict(slots_by_peer)
+        return self
+
+    def final_slots(self) -> Dict[int, int]:
+        return {int(self.tasks[name]["data"]["peer"]): slot for name, slot in self.sink_slots.items()}
+
+    # -- planning ---------------------------------------------------------------------------
+    def levelise(self) -> List[List[str]]:
+        """Kahn wavefronts: level(t) = 1 + max(level of inputs).  Source tasks are level 0
+        (`get_source_tasks`, dasklearn/tasks/dag.py:15-19)."""
+        indeg = {n: len(t["inputs"]) for n, t in self.tasks.items()}
+        frontier = [n for n, d in indeg.items() if d == 0]
+        levels: List[List[str]] = []
+        seen = 0
+        while frontier:
+            levels.append(frontier)
+            seen += len(frontier)
+            nxt: List[str] = []
+            for n in frontier:
+                for m, _idx in self.tasks[n]["outputs"]:
+                    indeg[m] -= 1
+                    if indeg[m] == 0:
+                        nxt.append(m)
+            frontier = nxt
+        if seen != len(self.tasks):
+            raise RuntimeError("compute graph has a cycle or dangling inputs (%d of %d tasks reachable)"
+                               % (seen, len(self.tasks)))
+        return levels
+
+    def plan(self):
+        ex = self.ex
+        ls = ex.settings.learning
+        value_slot: Dict[Tuple[str, int], int] = {}
+        sim_refs: Dict[int, int] = defaultdict(int)     # simulated reference counts during planning
+        for s_live in np.nonzero(ex.refs)[0]:
+            sim_refs[int(s_live)] = int(ex.refs[s_live])
+        free: List[int] = list(ex.free)
+        n_slots = ex.n_slots
+        extra = 0
+
+        def take() -> int:
+            nonlocal extra, n_slots
+            if not free:
+                free.append(n_slots)
+                n_slots += 1
+                extra += 1
+            return free.pop()
+
+        def drop(slot: int):
+            sim_refs[slot] -= 1
+            assert sim_refs[slot] >= 0
+            if sim_refs[slot] == 0:
+                free.append(slot)
+
+        for li, names in enumerate(self.levelise()):
+            by_func: Dict[str, Wave] = {}
+            # a level may hold two train tasks of one node only in malformed graphs; detect in executor
+            pending_release: List[int] = []
+            for name in names:
+                t = self.tasks[name]
+                d = t["data"]
+                if self.owned is not None and int(d["peer"]) not in self.owned:
+                    continue
+                w = by_func.get(t["func"])
+                if w is None:
+                    w = by_func[t["func"]] = Wave(li, t["func"])
+                n_cons = len(t["outputs"])
+                keep = n_cons if n_cons > 0 else 1          # sinks keep their row as the result
+                w.names.append(name)
+                w.peers.append(int(d["peer"]))
+                w.rounds.append(int(d.get("round", 0)))
+                w.times.append(int(d.get("time", 0)))
+                if t["func"] == "train":
+                    src = d["model"]
+                    if isinstance(src, tuple) and src[0] is None:
+                        src = None
+                    w.steps.append(int(d.get("local_steps", ls.local_steps)))
+                    if src is None and int(d["peer"]) in self.initial_models:
+                        slot = self.initial_models[int(d["peer"])]      # resume: train in place
+                        sim_refs[slot] -= 1
+                    elif src is None:                        # first round: (None, 0)
+                        slot = take()
+                        w.init_slots.append(slot)
+                    else:
+                        s_in = value_slot[tuple(src)]
+                        if sim_refs[s_in] == 1:              # sole consumer: train in place
+                            slot = s_in
+                            sim_refs[s_in] = 0
+                        else:
+                            slot = take()
+                            w.copy_src.append(s_in)
+                            w.copy_dst.append(slot)
+                            pending_release.append(s_in)
+                    w.in_slots.append(slot)
+                    w.out_slots.append(slot)
+                    sim_refs[slot] += keep
+                    value_slot[(name, 0)] = slot
+                elif t["func"] == "aggregate":
+                    ms = [value_slot[tuple(m)] for m in d["models"]]
+                    slot = take()
+                    w.model_slots.append(ms)
+                    w.weights.append(list(d["weights"]) if d.get("weights") else None)
+                    w.out_slots.append(slot)
+                    sim_refs[slot] += keep
+                    value_slot[(name, 0)] = slot
+                    pending_release.extend(ms)
+                else:                                        # test: identity on the model data path
+                    s_in = value_slot[tuple(d["model"])]
+                    w.in_slots.append(s_in)
+                    w.out_slots.append(s_in)
+                    sim_refs[s_in] += keep                   # alias first, then consume the input edge
+                    value_slot[(name, 0)] = s_in
+                    pending_release.append(s_in)
+                if n_cons == 0:
+                    self.sink_slots[name] = value_slot[(name, 0)]
+            # inputs are released only after the whole level ran (their rows are read by this level)
+            for s in pending_release:
+                drop(s)
+            order = [f for f in ("train", "aggregate", "test") if f in by_func]
+            for f in order:
+                self.waves.append(by_func[f])
+        if extra:
+            ex._grow(extra)
+        # host->device descriptors
+        for w in self.waves:
+            if w.func == "train":
+                w.prepared = ex.prepare_train(w.peers, w.rounds, w.steps)
+                self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:2] if hasattr(t, 'numel'))
+            elif w.func == "aggregate":
+                w.prepared = ex.prepare_aggregate(w.model_slots, w.out_slots, w.weights)
+                self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:5] if hasattr(t, 'numel'))
+        self._plan_free = free
+        self._plan_refs = dict(sim_refs)
+        self.planned = True
+        return self
+
+    # -- execution --------------------------------------------------------------------------
+    def run_wave(self, w: Wave, loss_out=None):
+        ex = self.ex
+        if w.func == "train":
+            ex.init_rows(w.init_slots)
+            ex.copy_rows(w.copy_src, w.copy_dst)
+            ex.train_wave(w.out_slots, w.peers, w.rounds, w.steps, prepared=w.prepared, loss_out=loss_out)
+        elif w.func == "aggregate":
+            ex.aggregate_wave(w.model_slots, w.out_slots, w.weights, variant=self.agg_variant,
+                              prepared=w.prepared)
+        else:
+            acc, loss = ex.test_wave(w.out_slots)
+            for i, name in enumerate(w.names):
+                ex.write_accuracy(w.peers[i], w.rounds[i], w.times[i], float(acc[i]), float(loss[i]))
+
+    def finish(self):
+        """Commit the planned pool state (free list, reference counts) to the executor."""
+        ex = self.ex
+        ex.free = list(self._plan_free)
+        ex.refs[:] = 0
+        for s, n in self._plan_refs.items():
+            if n > 0:
+                ex.refs[s] = n
+
+    def run(self, timing: bool = False):
+        if not self.planned:
+            self.plan()
+        ex = self.ex
+        results: Dict[str, List[RowHandle]] = {}
+        for w in self.waves:
+            if timing:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            self.run_wave(w)
+            if timing:
+                e1.record()
+                self.wave_times.append((w.func, len(w.names), e0, e1))
+            for name in w.names:
+                if name in self.sink_slots:
+                    res = [RowHandle(ex, self.sink_slots[name])]
+                    results[name] = res
+                    if self.on_sink:
+                        self.on_sink(name, res)
+        self.finish()
+        if timing:
+            torch.cuda.synchronize()
+            self.wave_times = [(f, n, e0.elapsed_time(e1)) for f, n, e0, e1 in self.wave_times]
+        return results
+
+    def run_with_loss(self):
+        """Run all waves; returns the device tensor `[steps, n_tasks]` of mean minibatch losses of
+        the last train wave (the step result a caller reads back)."""
+        if not self.planned:
+            self.plan()
+        loss = None
+        for w in self.waves:
+            if w.func == "train":
+                loss = torch.zeros((max(w.steps), len(w.names)), dtype=torch.float32, device=self.ex.device)
+                self.run_wave(w, loss_out=loss)
+            else:
+                self.run_wave(w)
+        return loss
+
+
+def solve(settings, serialized_tasks, dataset, on_sink=None, device=None, agg_variant: int = 0):
+    """One-call form: build the executor, plan and run the graph, return {sink task: [RowHandle]}."""
+    ex = WaveExecutor(settings, dataset, device=device)
+    solver = BatchedSolver(ex, serialized_tasks, on_sink=on_sink, agg_variant=agg_variant)
+    return solver.plan().run(), ex

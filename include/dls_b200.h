@@ -122,6 +122,24 @@ int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const int32_t *mode
                   float *out_logits /* optional [n_models][n_test][classes] */, int32_t precision,
                   void *workspace, int64_t workspace_bytes, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * test wave without a workspace argument.  This entry point has NO counterpart in the reference;
+ * it exists for callers that cannot allocate device memory (a foreign-function binding that only
+ * forwards model / image / result buffers, a monitoring thread while the solver owns the training
+ * workspace, a caller that must avoid cudaMalloc's device-wide synchronisation mid-round).
+ *
+ * Same outputs as dls_eval_wave (fp32 path, no logits).  The scratch memory is a fixed 32 MiB
+ * array inside the library, present on every GPU that loads it until the process exits; it
+ * limits a call to n_models <= 16 and n_test <= 4096, beyond which DLS_E_TOO_BIG is returned.
+ * The call itself performs no allocation of any kind.  All calls on a device share that array
+ * (it is re-initialised where needed at the start of each call), so calls that overlap on the
+ * GPU race with each other: issue them one after another.  The first call on each device
+ * resolves the array's address; make that first call outside of stream capture.
+ * ------------------------------------------------------------------------------------------ */
+int dls_eval_wave_noalloc(int32_t arch, const float *X, int64_t ldx, const int32_t *model_rows,
+                          int32_t n_models, const uint8_t *test_images, const int64_t *test_labels,
+                          int32_t n_test, int32_t *out_correct, double *out_loss_sum, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

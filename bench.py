@@ -254,7 +254,13 @@ def main():
     st = SessionSettings(participants=n_nodes, seed=42, data_dir=os.path.join(REPO, "gpurun_out", "bench_data"),
                          learning=LearningSettings(0.002, 0.9, 0.0, BATCH, LOCAL_STEPS), k=k, precision=args.precision)
     nbrs = synthetic.kreg_topology(n_nodes, k, seed=42)
-    owned = list(range(rank * args.nodes_per_gpu, (rank + 1) * args.nodes_per_gpu))
+    if world > 1:
+        from dls_b200.partition import DistributedSolver, partition_nodes
+        owner = partition_nodes(nbrs, world)
+        owned = [int(x) for x in np.nonzero(owner == rank)[0]]
+        assert len(owned) == args.nodes_per_gpu
+    else:
+        owner, owned = None, list(range(n_nodes))
     ds = DeviceDataset.synthetic(L, n_nodes, N_I, 256, dev, seed=42, node_ids=owned if world > 1 else None)
 
     def make_solver(n_rounds, name_offset=0, ex=None):
@@ -262,8 +268,7 @@ def main():
         if ex is None:
             ex = WaveExecutor(st, ds, device=dev, node_ids=owned if world > 1 else None)
         if world > 1:
-            from dls_b200.partition import DistributedSolver
-            return DistributedSolver(ex, dag, rank, world, args.nodes_per_gpu, agg_variant=args.agg_variant), ex
+            return DistributedSolver(ex, dag, rank, world, owner, agg_variant=args.agg_variant), ex
         return BatchedSolver(ex, dag, agg_variant=args.agg_variant), ex
 
     def barrier():
@@ -373,6 +378,11 @@ def main():
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": statistics.mean(e2e_ms)},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        if world > 1:
+            line["halo"] = {"bytes_per_gpu_per_wave": int(solver.halo_bytes // max(1, rounds)),
+                            "rows_per_gpu_per_wave": int(solver.max_halo),
+                            "transport": "NCCL all_to_all_single over NVLink, rows land in the tail of X",
+                            "note": "aggregate ms_per_wave includes the exchange"}
         if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
             v, cpu_agg_gbs, secs, steps, t_train, t_agg = cpu_sample(24, k + 1, 1, 4)

@@ -59,6 +59,8 @@ class WaveExecutor:
         n_local = len(ids)
         self.n_slots = n_slots or (2 * n_local + 2)
         ld = self.layout.ld
+        self.halo_rows = 0          # rows after the slot pool that receive other GPUs' models
+        self.sendbuf = None         # staging rows for the halo exchange
         self.X = torch.zeros((self.n_slots, ld), dtype=torch.float32, device=self.device)
         self.free: List[int] = list(range(self.n_slots - 1, -1, -1))
         self.refs = np.zeros(self.n_slots, dtype=np.int64)
@@ -75,13 +77,31 @@ class WaveExecutor:
             self._grow(max(n - len(self.free), self.n_slots // 2))
         return [self.free.pop() for _ in range(n)]
 
-    def _grow(self, extra: int):
-        X2 = torch.zeros((self.n_slots + extra, self.layout.ld), dtype=torch.float32, device=self.device)
-        X2[:self.n_slots].copy_(self.X)
-        self.X = X2
-        self.refs = np.concatenate([self.refs, np.zeros(extra, dtype=np.int64)])
-        self.free = list(range(self.n_slots + extra - 1, self.n_slots - 1, -1)) + self.free
-        self.n_slots += extra
+    def _grow(self, extra: int, halo_rows: int = None, send_rows: int = 0):
+        """Add `extra` pool slots and keep `halo_rows` receive rows after the pool (X is one
+        allocation so the aggregate kernel can index pool and halo rows alike)."""
+        halo_rows = self.halo_rows if halo_rows is None else max(halo_rows, self.halo_rows)
+        if extra or halo_rows != self.halo_rows:
+            X2 = torch.zeros((self.n_slots + extra + halo_rows, self.layout.ld), dtype=torch.float32,
+                             device=self.device)
+            X2[:self.n_slots].copy_(self.X[:self.n_slots])
+            self.X = X2
+            self.refs = np.concatenate([self.refs, np.zeros(extra, dtype=np.int64)])
+            self.free = list(range(self.n_slots + extra - 1, self.n_slots - 1, -1)) + self.free
+            self.n_slots += extra
+            self.halo_rows = halo_rows
+        if send_rows and (self.sendbuf is None or self.sendbuf.shape[0] < send_rows):
+            self.sendbuf = torch.empty((send_rows, self.layout.ld), dtype=torch.float32, device=self.device)
+
+    @property
+    def halo_base(self) -> int:
+        return self.n_slots
+
+    def gather_rows(self, slots_dev: torch.Tensor, n: int) -> torch.Tensor:
+        """Pack rows `slots` of X into the first n rows of the send buffer."""
+        dst = torch.arange(n, dtype=torch.int32, device=self.device)
+        K.copy_rows(self.X, self.sendbuf, slots_dev, dst, self.layout.P)
+        return self.sendbuf[:n]
 
     def retain(self, slot: int, n: int = 1):
         self.refs[slot] += n

@@ -1,0 +1,194 @@
+"""Multi-GPU solve: nodes are partitioned over the ranks of one box (one process per GPU); train
+and test waves need no communication; an aggregate wave first receives the neighbour rows that
+live on other GPUs ("halo") and then runs the same SpMM on pool + halo rows.
+
+The reference's analogue is the modulo client->broker map plus pickled `nn.Module` results sent
+broker to broker over ZeroMQ (`distribute_brokers` dasklearn/simulation/simulation.py:97-111,
+result routing dasklearn/broker.py:207-219); here rows move GPU to GPU over NVLink through one
+`all_to_all_single` per aggregate wave (NCCL; gloo in the CPU tests).
+
+Every rank holds the whole serialized DAG (as every broker does), so send and receive lists are
+derived locally and identically on all ranks from the `models` lists — the DAG is authoritative
+for topology, arrival order and churn.
+"""
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .solver import BatchedSolver, Wave
+
+
+def partition_nodes(in_neighbours: Sequence[Sequence[int]], world: int) -> np.ndarray:
+    """owner[node] in [0, world): greedy graph growing — every part is grown breadth-first inside
+    the still unassigned nodes, seeded next to the parts already built.  Keeps neighbourhoods
+    together: exact for rings (every part is one arc: 2 remote rows per GPU even after the
+    reference's random relabelling, dpsgd/simulation.py:37-41), a mild gain for sparse graphs;
+    random regular graphs are expanders — about (world-1)/world of their edges cross whatever we do."""
+    n = len(in_neighbours)
+    adj: List[set] = [set() for _ in range(n)]
+    for i, nb in enumerate(in_neighbours):
+        for j in nb:
+            adj[i].add(int(j)); adj[int(j)].add(i)
+    owner = -np.ones(n, dtype=np.int32)
+    per = (n + world - 1) // world
+    assigned_order: List[int] = []
+    for rank in range(world):
+        target = per if rank < world - 1 else n - len(assigned_order)
+        target = min(target, n - len(assigned_order))
+        size = 0
+        frontier: List[int] = []
+        while size < target:
+            if not frontier:
+                # seed: an unassigned node touching an assigned one (latest parts first), else lowest id
+                seed = -1
+                for u in reversed(assigned_order):
+                    cand = sorted(v for v in adj[u] if owner[v] < 0)
+                    if cand:
+                        seed = cand[0]
+                        break
+                if seed < 0:
+                    seed = int(np.nonzero(owner < 0)[0][0])
+                owner[seed] = rank
+                assigned_order.append(seed)
+                size += 1
+                frontier = [seed]
+                continue
+            nxt: List[int] = []
+            for u in frontier:
+                for v in sorted(adj[u]):
+                    if owner[v] < 0 and size < target:
+                        owner[v] = rank
+                        assigned_order.append(v)
+                        size += 1
+                        nxt.append(v)
+            frontier = nxt
+    return owner
+
+
+def block_partition(n: int, world: int) -> np.ndarray:
+    per = (n + world - 1) // world
+    return np.minimum(np.arange(n) // per, world - 1).astype(np.int32)
+
+
+def topology_from_dag(serialized_tasks: Sequence[Dict], n: int) -> List[List[int]]:
+    """In-neighbour lists read off the first aggregate task of every peer."""
+    peer_of = {t["name"]: int(t["data"]["peer"]) for t in serialized_tasks}
+    nb: List[Optional[List[int]]] = [None] * n
+    for t in serialized_tasks:
+        if t["func"] == "aggregate":
+            p = int(t["data"]["peer"])
+            if nb[p] is None:
+                nb[p] = [peer_of[m[0]] for m in t["data"]["models"] if peer_of[m[0]] != p]
+    return [x or [] for x in nb]
+
+
+class DistributedSolver(BatchedSolver):
+    def __init__(self, executor, serialized_tasks, rank: int, world: int, owner_of: Sequence[int],
+                 on_sink=None, agg_variant: int = 0, group=None):
+        owner_of = np.asarray(owner_of, dtype=np.int32)
+        owned = [int(p) for p in np.nonzero(owner_of == rank)[0]]
+        super().__init__(executor, serialized_tasks, on_sink=on_sink, owned_peers=owned, agg_variant=agg_variant)
+        self.rank, self.world, self.owner_of, self.group = rank, world, owner_of, group
+        self._halo_of: Dict[Tuple[str, int], int] = {}
+        self._level_xchg: Dict[int, dict] = {}
+        self.max_halo = 0
+        self.max_send = 0
+        self.halo_bytes = 0
+
+    # -- planning hooks ---------------------------------------------------------------------
+    def _owner_of_task(self, name: str) -> int:
+        return int(self.owner_of[int(self.tasks[name]["data"]["peer"])])
+
+    def _begin_level(self, level: int, names: List[str], pending_release: List[int]):
+        me = self.rank
+        recv: List[List[Tuple[str, int]]] = [[] for _ in range(self.world)]
+        send: List[List[int]] = [[] for _ in range(self.world)]
+        seen = set()
+        for name in names:
+            t = self.tasks[name]
+            q = self._owner_of_task(name)
+            if t["func"] != "aggregate":
+                for src, _ in t["inputs"]:
+                    if self._owner_of_task(src) != q:
+                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate"
+                                           % name)
+                continue
+            for m in t["data"]["models"]:
+                m = tuple(m)
+                r = self._owner_of_task(m[0])
+                if r == q:
+                    continue
+                if r == me:                                   # one reference per consuming remote task
+                    pending_release.append(self._value_slot[m])
+                if (q, m) in seen:
+                    continue
+                seen.add((q, m))
+                if q == me:
+                    recv[r].append(m)
+                if r == me:
+                    send[q].append(self._value_slot[m])
+        self._halo_of = {}
+        h = 0
+        for r in range(self.world):                           # all_to_all output is ordered by source rank
+            for m in recv[r]:
+                self._halo_of[m] = h
+                h += 1
+        n_send = sum(len(x) for x in send)
+        if h or n_send:
+            self._level_xchg[level] = {"send_slots": [s for x in send for s in x],
+                                       "send_counts": [len(x) for x in send],
+                                       "recv_counts": [len(x) for x in recv]}
+            self.max_halo = max(self.max_halo, h)
+            self.max_send = max(self.max_send, n_send)
+
+    def _model_slot(self, ref):
+        if ref in self._value_slot:
+            return self._value_slot[ref]
+        return -1 - self._halo_of[ref]                        # halo row, fixed up in _finish_plan
+
+    def _end_level_wave(self, level: int, wave: Wave):
+        if wave.func == "aggregate" and level in self._level_xchg:
+            wave.xchg = self._level_xchg[level]
+
+    def _finish_plan(self, extra_slots: int):
+        ex = self.ex
+        ex._grow(extra_slots, halo_rows=self.max_halo, send_rows=self.max_send)
+        base = ex.halo_base
+        # levels where this rank only sends (it owns no aggregate there) still take part in the exchange
+        have = {w.level for w in self.waves if getattr(w, "xchg", None)}
+        for level, x in self._level_xchg.items():
+            if level not in have:
+                w = Wave(level, "exchange")
+                w.xchg = x
+                pos = next((i for i, ww in enumerate(self.waves) if ww.level > level), len(self.waves))
+                self.waves.insert(pos, w)
+        for w in self.waves:
+            if w.func == "aggregate":
+                w.model_slots = [[s if s >= 0 else base + (-1 - s) for s in ms] for ms in w.model_slots]
+            x = getattr(w, "xchg", None)
+            if x:
+                x["send_idx"] = ex._dev_i32(x["send_slots"]) if x["send_slots"] else None
+                self.halo_bytes += sum(x["recv_counts"]) * ex.layout.P * 4
+
+    # -- execution --------------------------------------------------------------------------
+    def exchange(self, x: dict):
+        import torch.distributed as dist
+        ex = self.ex
+        ld = ex.layout.ld
+        n_send, n_recv = sum(x["send_counts"]), sum(x["recv_counts"])
+        if n_send:
+            sbuf = ex.gather_rows(x["send_idx"], n_send)
+        else:
+            sbuf = ex.X[0:0]
+        rbuf = ex.X[ex.halo_base: ex.halo_base + n_recv]
+        dist.all_to_all_single(rbuf.reshape(-1), sbuf.reshape(-1),
+                               output_split_sizes=[c * ld for c in x["recv_counts"]],
+                               input_split_sizes=[c * ld for c in x["send_counts"]], group=self.group)
+
+    def run_wave(self, w: Wave, loss_out=None):
+        x = getattr(w, "xchg", None)
+        if x:
+            self.exchange(x)
+        if w.func != "exchange":
+            super().run_wave(w, loss_out=loss_out)

@@ -26,7 +26,8 @@ SUPPORTED = ("train", "aggregate", "test")
 
 class Wave:
     __slots__ = ("level", "func", "names", "peers", "rounds", "times", "steps", "in_slots", "out_slots",
-                 "model_slots", "weights", "init_slots", "copy_src", "copy_dst", "release_after", "prepared")
+                 "model_slots", "weights", "init_slots", "copy_src", "copy_dst", "release_after", "prepared",
+                 "xchg")
 
     def __init__(self, level: int, func: str):
         self.level, self.func = level, func
@@ -44,6 +45,7 @@ class Wave:
         self.copy_dst: List[int] = []
         self.release_after: List[int] = []
         self.prepared = None
+        self.xchg = None            # multi-GPU: halo exchange that precedes this wave
 
 
 class BatchedSolver:
@@ -126,10 +128,12 @@ class BatchedSolver:
             if sim_refs[slot] == 0:
                 free.append(slot)
 
+        self._value_slot = value_slot
         for li, names in enumerate(self.levelise()):
             by_func: Dict[str, Wave] = {}
             # a level may hold two train tasks of one node only in malformed graphs; detect in executor
             pending_release: List[int] = []
+            self._begin_level(li, names, pending_release)
             for name in names:
                 t = self.tasks[name]
                 d = t["data"]
@@ -170,14 +174,14 @@ class BatchedSolver:
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
                 elif t["func"] == "aggregate":
-                    ms = [value_slot[tuple(m)] for m in d["models"]]
+                    ms = [self._model_slot(tuple(m)) for m in d["models"]]
                     slot = take()
                     w.model_slots.append(ms)
                     w.weights.append(list(d["weights"]) if d.get("weights") else None)
                     w.out_slots.append(slot)
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
-                    pending_release.extend(ms)
+                    pending_release.extend(x for x in ms if x >= 0)
                 else:                                        # test: identity on the model data path
                     s_in = value_slot[tuple(d["model"])]
                     w.in_slots.append(s_in)
@@ -192,9 +196,9 @@ class BatchedSolver:
                 drop(s)
             order = [f for f in ("train", "aggregate", "test") if f in by_func]
             for f in order:
+                self._end_level_wave(li, by_func[f])
                 self.waves.append(by_func[f])
-        if extra:
-            ex._grow(extra)
+        self._finish_plan(extra)
         # host->device descriptors
         for w in self.waves:
             if w.func == "train":
@@ -207,6 +211,20 @@ class BatchedSolver:
         self._plan_refs = dict(sim_refs)
         self.planned = True
         return self
+
+    # hooks overridden by the multi-GPU solver (partition.DistributedSolver)
+    def _begin_level(self, level: int, names: List[str], pending_release: List[int]):
+        pass
+
+    def _model_slot(self, ref: Tuple[str, int]) -> int:
+        return self._value_slot[ref]
+
+    def _end_level_wave(self, level: int, wave: Wave):
+        pass
+
+    def _finish_plan(self, extra_slots: int):
+        if extra_slots:
+            self.ex._grow(extra_slots)
 
     # -- execution --------------------------------------------------------------------------
     def run_wave(self, w: Wave, loss_out=None):

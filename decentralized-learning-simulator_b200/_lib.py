@@ -22,7 +22,7 @@ SIGNATURES = {
     "dls_build_info": (c_char_p, []),
     "dls_launch_count": (c_int64, []),
     "dls_agg_spmm_f32": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
-                                 c_void_p, c_void_p, c_int32, c_int32, c_int64, c_int32, c_void_p]),
+                                 c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int64, c_int32, c_void_p]),
     "dls_copy_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64,
                               c_void_p]),
     "dls_broadcast_row": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_void_p]),

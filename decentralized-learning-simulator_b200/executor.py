@@ -173,9 +173,20 @@ class WaveExecutor:
             return
         if prepared is None:
             prepared = self.prepare_aggregate(model_slots, out_slots, weights)
-        rowptr, colidx, wval, src_rows, out_rows, n_src = prepared
-        K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows, out_rows=out_rows,
-                   n_src_rows=n_src, variant=variant)
+        rowptr, colidx, wval, src_rows, out_rows, n_src, hint = prepared
+        # auto: shared-memory staged kernels when the wave fits (uniform fan-in -> specialised one),
+        # otherwise the L2 gather kernel.  The first launch of a wave shape settles the choice.
+        order = [variant] if variant else hint["order"]
+        for v in order:
+            try:
+                K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows,
+                           out_rows=out_rows, n_src_rows=n_src, variant=v)
+                if not variant:
+                    hint["order"] = [v]
+                break
+            except DlsError as exc:
+                if "DLS_E_SHAPE" not in str(exc) or v == order[-1]:
+                    raise
         self.stats["agg_rows"] += len(out_slots)
 
     def prepare_aggregate(self, model_slots, out_slots, weights=None):
@@ -197,11 +208,14 @@ class WaveExecutor:
         if set(src_index) & set(int(o) for o in out_slots):
             raise DlsError("aggregate wave would overwrite one of its own inputs")
         dev = self.device
+        fans = np.diff(rowptr)
+        uniform = len(fans) > 0 and int(fans.min()) == int(fans.max()) and 2 <= int(fans[0]) <= 16
+        hint = {"order": ([3] if uniform else []) + [2, 1]}
         return (torch.from_numpy(rowptr).to(dev, non_blocking=True),
                 torch.from_numpy(np.asarray(col, dtype=np.int32)).to(dev, non_blocking=True),
                 torch.from_numpy(np.asarray(w, dtype=np.float64).astype(np.float32)).to(dev, non_blocking=True),
                 torch.from_numpy(src_rows).to(dev, non_blocking=True),
-                self._dev_i32(out_slots), len(src_index))
+                self._dev_i32(out_slots), len(src_index), hint)
 
     def test_wave(self, slots: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
         """(accuracy %, mean loss) per slot on the whole test split

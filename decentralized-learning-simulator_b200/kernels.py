@@ -33,7 +33,7 @@ def agg_spmm(X: torch.Tensor, Y: torch.Tensor, rowptr, colidx, wval, P: int, src
         n_src_rows = src_rows.numel() if src_rows is not None else X.shape[0]
     rc = _lib.lib().dls_agg_spmm_f32(X.data_ptr(), X.stride(0), Y.data_ptr(), Y.stride(0),
                                      _i32(rowptr).data_ptr(), _i32(colidx).data_ptr(), wval.data_ptr(),
-                                     _lib.ptr(src_rows), _lib.ptr(out_rows), n_rows, n_src_rows, P, variant,
+                                     _lib.ptr(src_rows), _lib.ptr(out_rows), n_rows, n_src_rows, int(colidx.numel()), P, variant,
                                      _stream())
     _lib.check(rc, "dls_agg_spmm_f32")
 

@@ -54,14 +54,17 @@ int64_t     dls_launch_count(void);
  * evaluated per element in list order as acc = x_first*0; acc = fadd_rn(acc, fmul_rn(w, x))
  * (separate multiply and add, no FMA) — bit-identical to the reference's
  * `center.add_(w * p)` loop.  `src_rows` lists the n_src_rows distinct source rows of the wave
- * (NULL = identity: colidx indexes X directly); `out_rows == NULL` means row r.  X and Y may be
+ * (NULL = identity: colidx indexes X directly); `out_rows == NULL` means row r; `nnz` =
+ * rowptr[n_rows], the number of (colidx, wval) entries.  X and Y may be
  * the same allocation as long as no output row is also an input row of the same call.
- * `variant`: 0 = auto, 1 = gather through L2, 2 = shared-memory staged column tiles.
+ * `variant`: 0 = auto (gather), 1 = gather through L2, 2 = shared-memory staged column tiles,
+ * 3 = staged + the caller asserts a uniform fan-in F = nnz / n_rows in [2, 16] (rowptr[r] == r*F).
+ * 2 and 3 return DLS_E_SHAPE when the wave's source rows / CSR do not fit in shared memory.
  * ------------------------------------------------------------------------------------------ */
 int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t ldy,
                      const int32_t *rowptr, const int32_t *colidx, const float *wval,
                      const int32_t *src_rows, const int32_t *out_rows, int32_t n_rows,
-                     int32_t n_src_rows, int64_t P, int32_t variant, void *stream);
+                     int32_t n_src_rows, int32_t nnz, int64_t P, int32_t variant, void *stream);
 
 /* Row plumbing on the stacked tensor (replaces the pickle round-trip copies of
  * serialize_model/unserialize_model, dasklearn/models/__init__.py:9-16). */

@@ -60,7 +60,7 @@ class OracleExecutor(WaveExecutor):
             self.stats["train_steps"] += int((cnt[0] > 0).sum())
 
     def aggregate_wave(self, model_slots, out_slots, weights=None, variant=0, prepared=None):
-        rowptr, colidx, wval, src_rows, out_rows, n_src = prepared or self.prepare_aggregate(model_slots, out_slots,
+        rowptr, colidx, wval, src_rows, out_rows, n_src, _hint = prepared or self.prepare_aggregate(model_slots, out_slots,
                                                                                           weights)
         Xs = self.X[src_rows.long()].numpy()
         Y = O.fedavg_csr(Xs, rowptr.numpy(), colidx.numpy(), wval.numpy(), self.layout.P)

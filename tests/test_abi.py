@@ -36,5 +36,5 @@ def test_version_and_sizes():
 
 def test_argument_errors_without_gpu():
     l = _lib.lib()
-    assert l.dls_agg_spmm_f32(None, 0, None, 0, None, None, None, None, None, 1, 1, 4, 0, None) == -1
+    assert l.dls_agg_spmm_f32(None, 0, None, 0, None, None, None, None, None, 1, 1, 1, 4, 0, None) == -1
     assert l.dls_copy_rows(None, 0, None, 0, None, None, 1, 4, None) == -1

@@ -37,7 +37,7 @@ def _run(cuda, X, rowptr, col, w, P, variant, src_rows=None, out_rows=None, n_ou
     return Yd.cpu().numpy()
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("tag,fan,weighted", [("f5", 5, False), ("f11", 11, False), ("f2w", 2, True), ("f5w", 5, True)])
 def test_golden_fedavg(cuda, golden_dir, variant, tag, fan, weighted):
     """Same inputs as the reference-generated fixture: CUDA result == reference bits."""
@@ -50,7 +50,7 @@ def test_golden_fedavg(cuda, golden_dir, variant, tag, fan, weighted):
     assert np.array_equal(Y[0, :L.P].view(np.uint32), g[tag + "_y"].view(np.uint32))
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("n,k", [(16, 4), (64, 6), (200, 7)])
 def test_wave_vs_oracle(cuda, variant, n, k):
     """A whole D-PSGD aggregate wave on a k-regular topology, shuffled arrival order, own model last."""
@@ -128,6 +128,14 @@ def test_linearity_and_fixed_point_full_size(cuda):
     Y2 = torch.empty_like(Xd)
     K.agg_spmm(Xd, Y2, rowptr, perm, torch.ones(n, device=cuda), L.P, variant=2)
     assert torch.equal(Y2[:, :L.P], Y[:, :L.P])
+    # uniform fan-in 2 (node + one neighbour) at full size: variant 3 == variant 1 bit for bit
+    col2 = torch.stack([perm, torch.arange(n, dtype=torch.int32, device=cuda)], 1).reshape(-1).contiguous()
+    rp2 = torch.arange(n + 1, dtype=torch.int32, device=cuda) * 2
+    w2 = torch.full((2 * n,), 0.5, device=cuda)
+    Ya, Yb = torch.empty_like(Xd), torch.empty_like(Xd)
+    K.agg_spmm(Xd, Ya, rp2, col2, w2, L.P, variant=1)
+    K.agg_spmm(Xd, Yb, rp2, col2, w2, L.P, variant=3)
+    assert torch.equal(Ya[:, :L.P], Yb[:, :L.P])
 
 
 def test_copy_and_broadcast_rows(cuda):

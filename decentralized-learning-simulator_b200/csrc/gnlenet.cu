@@ -29,7 +29,8 @@ struct Carver {
     }
 };
 
-int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, bool backward, bool own_G)
+int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, bool backward, bool own_G,
+              int precision)
 {
     Carver c{reinterpret_cast<char *>(base), 0};
     const int64_t S = (int64_t)n_groups * gs;
@@ -41,6 +42,8 @@ int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, boo
     ws.glog = c.take<float>((int64_t)n_groups * 2);
     ws.prep = c.take<float>((int64_t)n_models * (PREP_SZ + 2400));
     ws.desc_i32 = c.take<int32_t>(S + 2 * (int64_t)n_groups + 16);
+    ws.precision = precision;
+    ws.prep_tc = precision == 1 ? (void *)c.take<uint16_t>((int64_t)n_models * TC_PREP_ELEMS) : nullptr;
     ws.p1 = ws.st1 = ws.st2 = ws.st3 = nullptr;
     ws.idx1 = ws.idx2 = ws.idx3 = nullptr;
     ws.da3 = ws.dc3 = ws.da2 = ws.dc2 = ws.da1 = ws.dp1 = ws.gnp = nullptr;
@@ -67,10 +70,10 @@ int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, boo
     return align_up(c.off, 256);
 }
 
-int64_t workspace_bytes(int n_groups, int gs, int n_models, bool backward, bool own_G)
+int64_t workspace_bytes(int n_groups, int gs, int n_models, bool backward, bool own_G, int precision)
 {
     Workspace ws;
-    return carve(ws, nullptr, n_groups, gs, n_models, backward, own_G);
+    return carve(ws, nullptr, n_groups, gs, n_models, backward, own_G, precision);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -111,11 +114,6 @@ prep_weights_kernel(Pass p, float *prep, int backward, const int32_t *model_acti
         }
         dst[i] = v;
     }
-}
-
-__device__ __forceinline__ const float *model_row(const Pass &p, int g, int &m) {
-    m = p.gmodel ? p.gmodel[g] : g;
-    return p.X + (int64_t)p.mrow[m] * p.ldx;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -742,6 +740,7 @@ int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st)
     const int32_t *active = p.gmodel ? nullptr : p.gcount;
     prep_weights_kernel<<<grid, 256, 0, st>>>(p, ws.prep, backward ? 1 : 0, active);
     DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) return prep_weights_tc(p, ws, backward, st);
     return 0;
 }
 
@@ -753,12 +752,20 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     const int sv = save ? 1 : 0;
     conv1_pool_gn_relu_kernel<<<S, 256, K1_SMEM_BYTES, st>>>(p, ws, sv);
     DLS_LAUNCH_CHECK();
-    conv5_kernel<32, 32, 15, true><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PO_W2T, OFF_B2);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv2_fwd_tc(p, ws, st))) return rc;
+    } else {
+        conv5_kernel<32, 32, 15, true><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PO_W2T, OFF_B2);
+        DLS_LAUNCH_CHECK();
+    }
     gn_pool_relu_kernel<32, 15, 7><<<S, 256, 0, st>>>(ws.c2, ws.a2, ws.st2, ws.idx2, p, OFF_G2W, OFF_G2B, sv);
     DLS_LAUNCH_CHECK();
-    conv5_kernel<32, 64, 7, true><<<S, 256, 11 * 11 * 32 * 4, st>>>(ws.a2, ws.c3, p, ws.prep, PO_W3T, OFF_B3);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv3_fwd_tc(p, ws, st))) return rc;
+    } else {
+        conv5_kernel<32, 64, 7, true><<<S, 256, 11 * 11 * 32 * 4, st>>>(ws.a2, ws.c3, p, ws.prep, PO_W3T, OFF_B3);
+        DLS_LAUNCH_CHECK();
+    }
     gn_pool_relu_kernel<64, 7, 3><<<S, 256, 0, st>>>(ws.c3, ws.a3, ws.st3, ws.idx3, p, OFF_G3W, OFF_G3B, sv);
     DLS_LAUNCH_CHECK();
     return 0;
@@ -785,8 +792,12 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     conv_wgrad_kernel<64, 7><<<dim3(p.n_groups, 4), 256, (11 * 11 * 32 + 49 * 16) * 4, st>>>(
         ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3);
     DLS_LAUNCH_CHECK();
-    conv5_kernel<64, 32, 7, false><<<S, 256, 11 * 11 * 64 * 4, st>>>(ws.dc3, ws.da2, p, ws.prep, PO_W3D, 0);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv3_dgrad_tc(p, ws, st))) return rc;
+    } else {
+        conv5_kernel<64, 32, 7, false><<<S, 256, 11 * 11 * 64 * 4, st>>>(ws.dc3, ws.da2, p, ws.prep, PO_W3D, 0);
+        DLS_LAUNCH_CHECK();
+    }
     // block 2
     gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
                                                            ws.gnp, p, OFF_G2W, 64);
@@ -794,8 +805,12 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     conv_wgrad_kernel<32, 15><<<dim3(p.n_groups, 2), 256, (19 * 19 * 32 + 225 * 16) * 4, st>>>(
         ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2);
     DLS_LAUNCH_CHECK();
-    conv5_kernel<32, 32, 15, false><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PO_W2D, 0);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv2_dgrad_tc(p, ws, st))) return rc;
+    } else {
+        conv5_kernel<32, 32, 15, false><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PO_W2D, 0);
+        DLS_LAUNCH_CHECK();
+    }
     // block 1 (GroupNorm -> ReLU after the pool), then the sparse conv1 weight gradient
     gn_block_bwd_kernel<32, 15, 15, false><<<S, 256, 0, st>>>(ws.da1, ws.a1, nullptr, ws.p1, ws.st1, ws.dp1,
                                                              ws.gnp, p, OFF_G1W, 0);

@@ -28,6 +28,7 @@ constexpr int A3_SZ = PH3 * PH3 * C3;   // 576
 constexpr int GNP_SZ = 2 * (C1 + C2 + C3);   // per-slot partial GN parameter gradients (256)
 
 constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
+constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)
 constexpr int PREP_SZ = 2 * W2T_SZ + 2 * W3T_SZ;   // W2t, W2d, W3t, W3d per model
 
 // All activations are NHWC fp32, one contiguous record per sample slot.
@@ -41,6 +42,8 @@ struct Workspace {
     float *G;                            // [n_groups][ldg] gradient rows (train) — may point to user memory
     int64_t ldg;
     float *prep;                         // [n_models][PREP_SZ]
+    void *prep_tc;                       // [n_models][TC_PREP_ELEMS] bf16, only when precision == 1
+    int precision;                       // 0 = fp32 CUDA cores, 1 = bf16 tcgen05 convolutions
     float *glog;                         // [n_groups][2] loss sum, correct count (eval) / loss (train)
     int32_t *desc_i32;                   // scratch for generated descriptors (eval)
 };
@@ -57,9 +60,22 @@ struct Pass {
     int64_t ldx;
 };
 
-int64_t workspace_bytes(int n_groups, int gs, int n_models, bool backward, bool own_G);
+__device__ __forceinline__ const float *model_row(const Pass &p, int g, int &m) {
+    m = p.gmodel ? p.gmodel[g] : g;
+    return p.X + (int64_t)p.mrow[m] * p.ldx;
+}
+
+int64_t workspace_bytes(int n_groups, int gs, int n_models, bool backward, bool own_G, int precision = 0);
 // Carves `base`; returns bytes used.
-int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, bool backward, bool own_G);
+int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, bool backward, bool own_G,
+              int precision = 0);
+
+// tensor-core (tcgen05) convolutions, tc_conv.cu
+int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);
+int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 
 int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);
 int forward(const Pass &p, Workspace &ws, bool save_for_backward, cudaStream_t st);

@@ -1,0 +1,251 @@
+// Tensor-core (tcgen05) implicit-GEMM 5x5 convolutions for GNLeNet, bf16 operands, fp32 TMEM
+// accumulators (precision 1).
+//
+// Implicit GEMM without im2col: the activations of SB samples are staged ONCE in shared memory as
+// bf16 "channel-chunk planes"  plane[c/8][padded pixel][8 channels]  (16 bytes per pixel).  In the
+// no-swizzle K-major UMMA layout a row of the A operand is 16 bytes and 8 consecutive rows are a
+// 128-byte core matrix — which is exactly 8 consecutive pixels of a plane.  So the A operand of
+// tap (ky,kx) for 128 consecutive output-pixel origins is just the plane address shifted by
+// (ky*PP + kx) pixels: 25 taps x CIN/16 MMAs (M=128, N=COUT, K=16) accumulate one output tile in
+// TMEM, reading the same staged bytes.  Origins are enumerated over the PADDED grid (PP = H+4
+// wide), so rows whose origin falls in the padding are computed and discarded (H=15: 62 % useful).
+//   A desc: start = plane(2h) + (tile*128 + ky*PP + kx)*16, LBO = plane stride, SBO = 128
+//   B desc: weights as [k/8][COUT][8] bf16 (k = tap*CIN + ci), LBO = COUT*16, SBO = 128
+// The same kernel computes the data gradient (input = dY, weights transposed + tap-flipped).
+#include "gnlenet.cuh"
+#include "tc_common.cuh"
+#include <cuda_bf16.h>
+
+namespace dls {
+namespace gnl {
+
+// bf16 UMMA-layout weight copies per model (elements):
+//   W2u [100][32][8] | W2ud [100][32][8] | W3u [100][64][8] | W3ud [200][32][8]
+constexpr int TCO_W2U = 0, TCO_W2UD = 25600, TCO_W3U = 51200, TCO_W3UD = 102400;
+
+__global__ void __launch_bounds__(256)
+prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t *model_active)
+{
+    const int m = blockIdx.y;
+    if (model_active && model_active[m] == 0) return;
+    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx;
+    __nv_bfloat16 *dst = prep + (int64_t)m * TC_PREP_ELEMS;
+    const int total = backward ? TC_PREP_ELEMS : TCO_W3UD;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        float v;
+        if (i < TCO_W2UD) {                       // W2u: k = tap*32 + ci ; [k/8][n=co][k%8]
+            const int e = i & 7, n = (i >> 3) & 31, kc = i >> 8, tap = kc >> 2, ci = (kc & 3) * 8 + e;
+            v = row[OFF_W2 + n * 800 + ci * 25 + tap];
+        } else if (i < TCO_W3U) {                 // W2ud: k = tap'*32 + co ; n = ci ; W2[co][ci][24-tap']
+            const int j = i - TCO_W2UD, e = j & 7, n = (j >> 3) & 31, kc = j >> 8, tap = kc >> 2,
+                      co = (kc & 3) * 8 + e;
+            v = row[OFF_W2 + co * 800 + n * 25 + (24 - tap)];
+        } else if (i < TCO_W3UD) {                // W3u: k = tap*32 + ci ; n = co (64)
+            const int j = i - TCO_W3U, e = j & 7, n = (j >> 3) & 63, kc = j >> 9, tap = kc >> 2,
+                      ci = (kc & 3) * 8 + e;
+            v = row[OFF_W3 + n * 800 + ci * 25 + tap];
+        } else {                                  // W3ud: k = tap'*64 + co ; n = ci (32) ; W3[co][ci][24-tap']
+            const int j = i - TCO_W3UD, e = j & 7, n = (j >> 3) & 31, kc = j >> 8, tap = kc >> 3,
+                      co = (kc & 7) * 8 + e;
+            v = row[OFF_W3 + co * 800 + n * 25 + (24 - tap)];
+        }
+        dst[i] = __float2bfloat16_rn(v);
+    }
+}
+
+template <int CIN, int COUT, int H, int SB>
+struct ConvTcCfg {
+    static constexpr int PP = H + 4;
+    static constexpr int NPS = PP * PP;                    // padded pixels per sample
+    static constexpr int LAST = (H - 1) * PP + H;          // origins needed in the last sample
+    static constexpr int TAIL = 4 * PP + 4;                // furthest tap shift
+    static constexpr int NPIX = ((SB * NPS + TAIL + 128 + 7) / 8) * 8;   // + one tile of slack for the last M tile
+    static constexpr int PLANE = NPIX * 16;                // bytes
+    static constexpr int NCH = CIN / 8;
+    static constexpr int KCH = 25 * NCH;                   // 8-element K chunks
+    static constexpr int B_BYTES = KCH * COUT * 16;
+    static constexpr int A_BYTES = NCH * PLANE;
+    static constexpr int SMEM = B_BYTES + A_BYTES + COUT * 4 + 64;
+    static constexpr int TMEM_COLS = (2 * COUT <= 64) ? 64 : 128;
+};
+
+template <int CIN, int COUT, int H, int SB, bool BIAS>
+__global__ void __launch_bounds__(128, 1)
+conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
+               const __nv_bfloat16 *__restrict__ wprep, int wprep_off, int bias_off)
+{
+    using C = ConvTcCfg<CIN, COUT, H, SB>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *sB = smem;
+    uint8_t *sA = smem + C::B_BYTES;
+    float *sbias = reinterpret_cast<float *>(sA + C::A_BYTES);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sbias + COUT);       // 2 mbarriers
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int chunks = (p.gs + SB - 1) / SB;
+    const int g = blockIdx.x / chunks, chunk = blockIdx.x - g * chunks;
+    const int s0 = chunk * SB;
+    const int cnt = p.gcount[g];
+    if (cnt <= 0) return;
+    int n_s = p.gs - s0;
+    if (n_s > SB) n_s = SB;
+    // active samples of this chunk (empty slots carry img_idx < 0; they are always at the tail)
+    int n_act = 0;
+    for (int s = 0; s < n_s; ++s) n_act += (p.img_idx[g * p.gs + s0 + s] >= 0) ? 1 : 0;
+    if (n_act == 0) return;
+    int m;
+    const float *row = model_row(p, g, m);
+
+    // ---- stage weights (already in UMMA layout) and activations (fp32 NHWC -> bf16 planes) ----
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(wprep + (int64_t)m * TC_PREP_ELEMS + wprep_off);
+        uint4 *dst = reinterpret_cast<uint4 *>(sB);
+        for (int i = t; i < C::B_BYTES / 16; i += 128) dst[i] = __ldg(src + i);
+        uint4 *za = reinterpret_cast<uint4 *>(sA);
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = t; i < C::A_BYTES / 16; i += 128) za[i] = z;
+        if (t < COUT) sbias[t] = BIAS ? row[bias_off + t] : 0.f;
+    }
+    if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    __syncthreads();
+    for (int s = 0; s < n_s; ++s) {
+        const int slot = g * p.gs + s0 + s;
+        if (p.img_idx[slot] < 0) continue;
+        const float *src = in + (int64_t)slot * (H * H * CIN);
+        for (int i = t; i < H * H * C::NCH; i += 128) {
+            const int pix = i / C::NCH, ch = i - pix * C::NCH;
+            const int y = pix / H, x = pix - y * H;
+            const float4 a = *reinterpret_cast<const float4 *>(src + pix * CIN + ch * 8);
+            const float4 b = *reinterpret_cast<const float4 *>(src + pix * CIN + ch * 8 + 4);
+            __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
+            __nv_bfloat162 q2 = __floats2bfloat162_rn(b.x, b.y), q3 = __floats2bfloat162_rn(b.z, b.w);
+            uint4 v;
+            v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
+            v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
+            const int pp = s * C::NPS + (y + 2) * C::PP + (x + 2);
+            *reinterpret_cast<uint4 *>(sA + ch * C::PLANE + pp * 16) = v;
+        }
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t a_base = tc::smem_u32(sA), b_base = tc::smem_u32(sB);
+    const uint32_t idesc = tc::instr_desc_bf16(128, COUT, 0, 0);
+    const int n_origins = (n_s - 1) * C::NPS + C::LAST;
+    const int n_tiles = (n_origins + 127) / 128;
+
+    auto issue = [&](int tile) {
+        const uint32_t d = tmem + (uint32_t)((tile & 1) * COUT);
+        uint32_t acc = 0;
+#pragma unroll 1
+        for (int tap = 0; tap < 25; ++tap) {
+            const int ky = tap / 5, kx = tap - ky * 5;
+            const uint32_t a_tap = a_base + (uint32_t)(tile * 128 + ky * C::PP + kx) * 16;
+#pragma unroll
+            for (int h = 0; h < CIN / 16; ++h) {
+                const uint64_t ad = tc::smem_desc(a_tap + (uint32_t)(2 * h) * C::PLANE, C::PLANE, 128);
+                const uint64_t bd = tc::smem_desc(b_base + (uint32_t)(tap * C::NCH + 2 * h) * (COUT * 16),
+                                                  COUT * 16, 128);
+                tc::mma_f16(d, ad, bd, idesc, acc);
+                acc = 1;
+            }
+        }
+        tc::mma_commit(&bars[tile & 1]);
+    };
+
+    if (t == 0) issue(0);
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        if (t == 0 && tile + 1 < n_tiles) issue(tile + 1);
+        __syncwarp();
+        tc::mbar_wait(&bars[tile & 1], (uint32_t)((tile >> 1) & 1));
+        tc::fence_after_sync();
+        const int o = tile * 128 + t;                       // origin handled by this thread (TMEM lane t)
+        const int s = o / C::NPS, loc = o - s * C::NPS;
+        const int oy = loc / C::PP, ox = loc - oy * C::PP;
+        const bool valid = (s < n_s) && (oy < H) && (ox < H) && (p.img_idx[g * p.gs + s0 + (s < n_s ? s : 0)] >= 0);
+        float *dst = out + (int64_t)(g * p.gs + s0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
+#pragma unroll
+        for (int c0 = 0; c0 < COUT; c0 += 32) {
+            uint32_t r[32];
+            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((tile & 1) * COUT + c0), r);
+            tc::tmem_ld_wait();
+            if (valid) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    float4 v;
+                    v.x = __uint_as_float(r[j]) + sbias[c0 + j];
+                    v.y = __uint_as_float(r[j + 1]) + sbias[c0 + j + 1];
+                    v.z = __uint_as_float(r[j + 2]) + sbias[c0 + j + 2];
+                    v.w = __uint_as_float(r[j + 3]) + sbias[c0 + j + 3];
+                    *reinterpret_cast<float4 *>(dst + c0 + j) = v;
+                }
+            }
+        }
+        tc::fence_before_sync();
+        __syncthreads();                                    // everyone done with this TMEM buffer
+        tc::fence_after_sync();
+    }
+    if (warp == 0) tc::tmem_dealloc(tmem, C::TMEM_COLS);
+    (void)lane;
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+template <int CIN, int COUT, int H, int SB, bool BIAS>
+static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv_bfloat16 *wprep, int wprep_off,
+                          int bias_off, cudaStream_t st)
+{
+    using C = ConvTcCfg<CIN, COUT, H, SB>;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<CIN, COUT, H, SB, BIAS>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    const int chunks = (p.gs + SB - 1) / SB;
+    conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * chunks, 128, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
+                                                                                    bias_off);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st)
+{
+    dim3 grid(8, p.n_models);
+    const int32_t *active = p.gmodel ? nullptr : p.gcount;
+    prep_weights_tc_kernel<<<grid, 256, 0, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
+                                                 active);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_conv_tc<32, 32, 15, 4, true>(ws.a1, ws.c2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+                                               TCO_W2U, OFF_B2, st);
+}
+int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_conv_tc<32, 64, 7, 8, true>(ws.a2, ws.c3, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+                                              TCO_W3U, OFF_B3, st);
+}
+int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_conv_tc<64, 32, 7, 4, false>(ws.dc3, ws.da2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+                                               TCO_W3UD, 0, st);
+}
+int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_conv_tc<32, 32, 15, 4, false>(ws.dc2, ws.da1, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+                                                TCO_W2UD, 0, st);
+}
+
+}  // namespace gnl
+}  // namespace dls

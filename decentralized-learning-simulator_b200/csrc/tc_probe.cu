@@ -1,0 +1,67 @@
+// dls_tc_probe — runs a caller-described sequence of tcgen05.mma instructions on caller-provided
+// shared-memory operand images and returns the accumulator tile from TMEM.  It pins down the
+// descriptor encodings (tests/test_gpu_tc_probe.py) that the tensor-core convolution kernels use.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace dls {
+
+__global__ void __launch_bounds__(128)
+tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *__restrict__ b_img, int b_bytes,
+                const uint64_t *__restrict__ a_desc, const uint64_t *__restrict__ b_desc, int n_mma,
+                uint32_t idesc, int ncols, float *__restrict__ out)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    uint8_t *sa = smem;
+    uint8_t *sb = smem + ((a_bytes + 1023) & ~1023);
+    const int t = threadIdx.x, warp = t >> 5;
+    for (int i = t; i < a_bytes; i += 128) sa[i] = a_img[i];
+    for (int i = t; i < b_bytes; i += 128) sb[i] = b_img[i];
+    if (t == 0) { tc::mbar_init(&bar, 1); tc::mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc(&tmem_base, 64);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tm = tmem_base;
+    if (t == 0) {
+        const uint32_t abase = tc::smem_u32(sa) >> 4, bbase = tc::smem_u32(sb) >> 4;
+        for (int i = 0; i < n_mma; ++i)
+            tc::mma_f16(tm, a_desc[i] + abase, b_desc[i] + bbase, idesc, i > 0 ? 1u : 0u);
+        tc::mma_commit(&bar);
+    }
+    tc::mbar_wait(&bar, 0);
+    tc::fence_after_sync();
+    uint32_t r[32];
+    for (int c0 = 0; c0 < ncols; c0 += 32) {
+        tc::tmem_ld32(tm + ((uint32_t)(warp * 32) << 16) + c0, r);
+        tc::tmem_ld_wait();
+        for (int j = 0; j < 32 && c0 + j < ncols; ++j) out[(size_t)t * ncols + c0 + j] = __uint_as_float(r[j]);
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tm, 64);
+}
+
+}  // namespace dls
+
+using namespace dls;
+
+// a_desc / b_desc: descriptors with start-address field RELATIVE to the operand image (the kernel
+// adds the image's shared-memory address); out: [128 TMEM lanes][ncols] floats, ncols <= 64.
+extern "C" int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, int32_t b_bytes,
+                            const uint64_t *a_desc, const uint64_t *b_desc, int32_t n_mma, uint32_t idesc,
+                            int32_t ncols, float *out, void *stream)
+{
+    if (!a_img || !b_img || !a_desc || !b_desc || !out || n_mma <= 0 || ncols <= 0 || ncols > 64) return DLS_E_ARG;
+    const size_t smem = ((size_t)(a_bytes + 1023) & ~(size_t)1023) + (size_t)b_bytes + 1024;
+    if (smem > 200 * 1024) return DLS_E_TOO_BIG;
+    cudaError_t e = cudaFuncSetAttribute(tc_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    tc_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(a_img, a_bytes, b_img, b_bytes, a_desc, b_desc, n_mma,
+                                                            idesc, ncols, out);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}

@@ -83,7 +83,8 @@ static int check_rows(const void *X, int64_t ld, int64_t P)
 extern "C" int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int32_t batch)
 {
     if (n_tasks < 0 || batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
-    if (arch == DLS_ARCH_GNLENET) return gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true);
+    // sized for either precision (the tensor-core path adds bf16 weight copies)
+    if (arch == DLS_ARCH_GNLENET) return gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true, 1);
     return DLS_E_SHAPE;
 }
 
@@ -106,7 +107,7 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
                               int64_t workspace_bytes, void *stream)
 {
     if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
-    if (precision != 0) return DLS_E_SHAPE;
+    if (precision != 0 && precision != 1) return DLS_E_SHAPE;
     if (!task_row || !task_peer || !images || !labels || !mb_index || !mb_count || !workspace ||
         n_tasks < 0 || n_steps < 0)
         return DLS_E_ARG;
@@ -118,10 +119,10 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
         if (!mom_first) return DLS_E_ARG;
     }
     if (n_tasks == 0 || n_steps == 0) return 0;
-    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true)) return DLS_E_WS;
+    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true, precision)) return DLS_E_WS;
     cudaStream_t st = (cudaStream_t)stream;
     gnl::Workspace ws;
-    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, true);
+    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, true, precision);
     for (int s = 0; s < n_steps; ++s) {
         gnl::Pass p;
         p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks;
@@ -145,7 +146,7 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
                              int64_t workspace_bytes, void *stream)
 {
     if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
-    if (precision != 0) return DLS_E_SHAPE;
+    if (precision != 0 && precision != 1) return DLS_E_SHAPE;
     if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0)
         return DLS_E_ARG;
     if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
@@ -153,9 +154,9 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
     if (rc) return rc;
     if ((rc = check_rows(G, ldg, gnl::P))) return rc;
     if (n_tasks == 0) return 0;
-    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, false)) return DLS_E_WS;
+    if (workspace_bytes < gnl::workspace_bytes(n_tasks, batch, n_tasks, true, false, precision)) return DLS_E_WS;
     gnl::Workspace ws;
-    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, false);
+    gnl::carve(ws, workspace, n_tasks, batch, n_tasks, true, false, precision);
     ws.G = G; ws.ldg = ldg;
     gnl::Pass p;
     p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks;
@@ -170,7 +171,7 @@ extern "C" int64_t dls_eval_workspace_bytes(int32_t arch, int32_t n_models, int3
     const int gpm = (n_test + EVAL_GS - 1) / EVAL_GS;
     const int64_t total_groups = (int64_t)n_models * gpm;
     const int chunk = (int)(total_groups < EVAL_CHUNK_GROUPS ? total_groups : EVAL_CHUNK_GROUPS);
-    return gnl::workspace_bytes(chunk > 0 ? chunk : 1, EVAL_GS, n_models, false, false) +
+    return gnl::workspace_bytes(chunk > 0 ? chunk : 1, EVAL_GS, n_models, false, false, 1) +
            total_groups * 2 * (int64_t)sizeof(float) + 1024;
 }
 
@@ -181,7 +182,7 @@ extern "C" int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const in
                              int64_t workspace_bytes, void *stream)
 {
     if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
-    if (precision != 0) return DLS_E_SHAPE;
+    if (precision != 0 && precision != 1) return DLS_E_SHAPE;
     if (!model_rows || !test_images || !test_labels || !out_correct || !out_loss_sum || !workspace ||
         n_models < 0 || n_test < 0)
         return DLS_E_ARG;
@@ -194,7 +195,7 @@ extern "C" int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const in
     const int64_t total_groups = (int64_t)n_models * gpm;
     const int chunk = (int)(total_groups < EVAL_CHUNK_GROUPS ? total_groups : EVAL_CHUNK_GROUPS);
     gnl::Workspace ws;
-    const int64_t used = gnl::carve(ws, workspace, chunk, EVAL_GS, n_models, false, false);
+    const int64_t used = gnl::carve(ws, workspace, chunk, EVAL_GS, n_models, false, false, precision);
     float *glog_all = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + used);
     int32_t *d_img_idx = ws.desc_i32;
     int32_t *d_gmodel = ws.desc_i32 + (int64_t)chunk * EVAL_GS;

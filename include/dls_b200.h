@@ -125,6 +125,14 @@ int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const int32_t *mode
                   float *out_logits /* optional [n_models][n_test][classes] */, int32_t precision,
                   void *workspace, int64_t workspace_bytes, void *stream);
 
+/* Diagnostic: run `n_mma` tcgen05.mma (kind::f16, bf16 operands, fp32 accumulate) instructions on
+ * caller-provided shared-memory operand images and return the TMEM accumulator [128 lanes][ncols].
+ * Used by the tests to pin the descriptor encodings of the tensor-core convolution kernels.
+ * No reference counterpart. */
+int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, int32_t b_bytes,
+                 const uint64_t *a_desc, const uint64_t *b_desc, int32_t n_mma, uint32_t idesc,
+                 int32_t ncols, float *out, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * test wave without a workspace argument.  This entry point has NO counterpart in the reference;
  * it exists for callers that cannot allocate device memory (a foreign-function binding that only

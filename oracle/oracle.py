@@ -104,6 +104,51 @@ def gnlenet_forward(p, x):
     return F.log_softmax(x, dim=1)
 
 
+def bf16r(t: torch.Tensor) -> torch.Tensor:
+    """Round fp32 values to bf16 (nearest even) and back: what a tensor-core operand sees."""
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+class _ConvBf16(torch.autograd.Function):
+    """5x5/pad-2 convolution as the precision-1 (tcgen05) kernels compute it: operands rounded to
+    bf16, products accumulated in fp32.  forward: conv(bf16(x), bf16(w)) + b;  data gradient:
+    conv_transpose(bf16(dy), bf16(w));  weight gradient: from bf16(dy), bf16(x) when `wgrad_bf16`
+    (tensor-core weight-gradient kernel) else from the fp32 tensors (CUDA-core kernel)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, wgrad_bf16):
+        ctx.save_for_backward(x, w)
+        ctx.wgrad_bf16 = wgrad_bf16
+        return F.conv2d(bf16r(x), bf16r(w), b, padding=2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dx = torch.nn.grad.conv2d_input(x.shape, bf16r(w), bf16r(dy), padding=2)
+        if ctx.wgrad_bf16:
+            dw = torch.nn.grad.conv2d_weight(bf16r(x), w.shape, bf16r(dy), padding=2)
+        else:
+            dw = torch.nn.grad.conv2d_weight(x, w.shape, dy, padding=2)
+        return dx, dw, dy.sum(dim=(0, 2, 3)), None
+
+
+def gnlenet_forward_bf16(p, x, wgrad_bf16=False):
+    """GNLeNet with conv2/conv3 evaluated like the precision-1 kernels (conv1, GroupNorm, pooling,
+    classifier stay fp32).  Used to separate implementation errors from bf16 rounding effects."""
+    x = F.conv2d(x, p["features.0.weight"], p["features.0.bias"], padding=2)
+    x = F.max_pool2d(x, 3, 2)
+    x = F.relu(F.group_norm(x, 2, p["features.2.weight"], p["features.2.bias"], eps=1e-5))
+    x = _ConvBf16.apply(x, p["features.4.weight"], p["features.4.bias"], wgrad_bf16)
+    x = F.group_norm(x, 2, p["features.5.weight"], p["features.5.bias"], eps=1e-5)
+    x = F.relu(F.max_pool2d(x, 3, 2))
+    x = _ConvBf16.apply(x, p["features.8.weight"], p["features.8.bias"], wgrad_bf16)
+    x = F.group_norm(x, 2, p["features.9.weight"], p["features.9.bias"], eps=1e-5)
+    x = F.relu(F.max_pool2d(x, 3, 2))
+    x = torch.flatten(x, 1)
+    x = F.linear(x, p["classifier.0.weight"], p["classifier.0.bias"])
+    return F.log_softmax(x, dim=1)
+
+
 def femnist_forward(p, x):
     """x: [B,1,28,28]; logits out (femnist.py:80-85)."""
     x = F.max_pool2d(F.relu(F.conv2d(x, p["conv1.weight"], p["conv1.bias"], padding=2)), 2, 2)
@@ -181,11 +226,16 @@ def train_task(layout, row: np.ndarray, mom: Optional[np.ndarray], images_u8: np
     return new_row, new_mom, losses
 
 
-def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarray) -> Tuple[np.ndarray, float]:
-    """Mean-loss gradient of one minibatch (used to check the backward kernels in isolation)."""
+def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarray, emulate_bf16: bool = False,
+                wgrad_bf16: bool = False) -> Tuple[np.ndarray, float]:
+    """Mean-loss gradient of one minibatch (used to check the backward kernels in isolation).
+    `emulate_bf16`: evaluate conv2/conv3 with bf16-rounded operands like the precision-1 kernels."""
     P = layout.P
     wl = torch.from_numpy(np.array(row[:P], dtype=np.float32, copy=True)).requires_grad_(True)
-    out = forward(layout, wl, to_tensor(images_u8))
+    if emulate_bf16:
+        out = gnlenet_forward_bf16(_views(layout, wl), to_tensor(images_u8), wgrad_bf16)
+    else:
+        out = forward(layout, wl, to_tensor(images_u8))
     loss = loss_fn(layout, out, torch.from_numpy(labels.astype(np.int64)))
     loss.backward()
     return wl.grad.numpy().copy(), float(loss.detach())

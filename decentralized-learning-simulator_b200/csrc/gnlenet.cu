@@ -789,9 +789,13 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
                                                           ws.gnp, p, OFF_G3W, 128);
     DLS_LAUNCH_CHECK();
-    conv_wgrad_kernel<64, 7><<<dim3(p.n_groups, 4), 256, (11 * 11 * 32 + 49 * 16) * 4, st>>>(
-        ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv3_wgrad_tc(p, ws, st))) return rc;
+    } else {
+        conv_wgrad_kernel<64, 7><<<dim3(p.n_groups, 4), 256, (11 * 11 * 32 + 49 * 16) * 4, st>>>(
+            ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3);
+        DLS_LAUNCH_CHECK();
+    }
     if (ws.precision == 1) {
         if ((rc = conv3_dgrad_tc(p, ws, st))) return rc;
     } else {
@@ -802,9 +806,13 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
                                                            ws.gnp, p, OFF_G2W, 64);
     DLS_LAUNCH_CHECK();
-    conv_wgrad_kernel<32, 15><<<dim3(p.n_groups, 2), 256, (19 * 19 * 32 + 225 * 16) * 4, st>>>(
-        ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv2_wgrad_tc(p, ws, st))) return rc;
+    } else {
+        conv_wgrad_kernel<32, 15><<<dim3(p.n_groups, 2), 256, (19 * 19 * 32 + 225 * 16) * 4, st>>>(
+            ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2);
+        DLS_LAUNCH_CHECK();
+    }
     if (ws.precision == 1) {
         if ((rc = conv2_dgrad_tc(p, ws, st))) return rc;
     } else {

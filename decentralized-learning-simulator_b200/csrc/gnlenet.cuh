@@ -76,6 +76,8 @@ int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 
 int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);
 int forward(const Pass &p, Workspace &ws, bool save_for_backward, cudaStream_t st);

@@ -247,5 +247,214 @@ int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
                                                 TCO_W2UD, 0, st);
 }
 
+
+// ==========================================================================================
+// Weight gradient on tensor cores.
+//   dW[co][ci][tap] = sum over samples s and output pixels q of dY[s][q][co] * in[s][q + shift(tap)][ci]
+// As a GEMM per tap: D[co, ci] = A^T-form with the PIXEL index as the reduction (K) dimension.
+// Both operands are staged as bf16 channel-chunk planes  plane[c/8][pixel][8]  in which the M/N
+// index (channel) is the contiguous one, i.e. they are "MN-major" UMMA operands:
+//   A = dY   (M = 64 output channels; conv2 has 32 -> planes 4..7 are zero), LBO = 128, SBO = plane
+//   B = in   (N = 32 input channels), start shifted by the tap, LBO = 128, SBO = plane
+// Pixels are enumerated over the padded grid (like the forward kernel); dY is zero at origins that
+// fall into the padding, so those terms vanish.  One CTA = one node x one half of the 25 taps
+// (13 x 32 fp32 TMEM columns); it walks over all samples of the node, double buffering the
+// staged planes: warps 1-7 stage chunk c+1 while one thread of warp 0 issues the MMAs of chunk c.
+// ==========================================================================================
+template <int COUT, int H, int SB>
+struct WgradTcCfg {
+    static constexpr int CIN = 32;
+    static constexpr int PP = H + 4;
+    static constexpr int NPS = PP * PP;
+    static constexpr int KPIX = ((SB * NPS + 15) / 16) * 16;       // reduction length per chunk
+    static constexpr int TAIL = ((4 * PP + 4 + 7) / 8) * 8;
+    static constexpr int NPD = KPIX, NPI = KPIX + TAIL;
+    static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
+    static constexpr int BUF = 8 * PLANE_D + 4 * PLANE_I;
+    static constexpr int SMEM = 2 * BUF + 128;
+    static constexpr int TAPS0 = 13;                                // taps of CTA half 0; half 1 gets 12
+};
+
+constexpr int WG_THREADS = 256;
+constexpr int WG_PRODUCERS = WG_THREADS - 32;
+
+template <int COUT, int H, int SB>
+__global__ void __launch_bounds__(WG_THREADS, 1)
+conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws, int w_off)
+{
+    using C = WgradTcCfg<COUT, H, SB>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + 2 * C::BUF);   // full[2], empty[2], done
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int g = blockIdx.x >> 1, half = blockIdx.x & 1;
+    if (p.gcount[g] <= 0) return;
+    const int tap0 = half ? C::TAPS0 : 0, ntap = half ? 25 - C::TAPS0 : C::TAPS0;
+    const int gs = p.gs, n_chunks = (gs + SB - 1) / SB;
+
+    {   // zero both buffers once: padding borders, K tail and (conv2) the four unused dY planes stay zero
+        uint4 *z = reinterpret_cast<uint4 *>(smem);
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = t; i < 2 * C::BUF / 16; i += WG_THREADS) z[i] = zero;
+    }
+    if (t == 0) {
+        tc::mbar_init(&bars[0], WG_PRODUCERS); tc::mbar_init(&bars[1], WG_PRODUCERS);
+        tc::mbar_init(&bars[2], 1); tc::mbar_init(&bars[3], 1); tc::mbar_init(&bars[4], 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp >= 1) {
+        // ------------------------------ producers ------------------------------
+        const int pt = t - 32;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b = c & 1;
+            if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));   // MMAs of chunk c-2 done
+            uint8_t *sD = smem + b * C::BUF;
+            uint8_t *sI = sD + 8 * C::PLANE_D;
+            for (int i = pt; i < SB * C::NPS * (COUT / 8); i += WG_PRODUCERS) {
+                const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
+                const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
+                const int sl = c * SB + s;
+                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                if (sl < gs && oy < H && ox < H && p.img_idx[g * gs + sl] >= 0) {
+                    const float *src = dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8;
+                    const float4 a = *reinterpret_cast<const float4 *>(src);
+                    const float4 bb = *reinterpret_cast<const float4 *>(src + 4);
+                    __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
+                    __nv_bfloat162 q2 = __floats2bfloat162_rn(bb.x, bb.y), q3 = __floats2bfloat162_rn(bb.z, bb.w);
+                    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
+                    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
+                }
+                *reinterpret_cast<uint4 *>(sD + ch * C::PLANE_D + pix * 16) = v;
+            }
+            for (int i = pt; i < SB * H * H * 4; i += WG_PRODUCERS) {
+                const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
+                const int y = pix / H, x = pix - y * H;
+                const int sl = c * SB + s;
+                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                if (sl < gs && p.img_idx[g * gs + sl] >= 0) {
+                    const float *src = in + (int64_t)(g * gs + sl) * (H * H * 32) + pix * 32 + ch * 8;
+                    const float4 a = *reinterpret_cast<const float4 *>(src);
+                    const float4 bb = *reinterpret_cast<const float4 *>(src + 4);
+                    __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
+                    __nv_bfloat162 q2 = __floats2bfloat162_rn(bb.x, bb.y), q3 = __floats2bfloat162_rn(bb.z, bb.w);
+                    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
+                    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
+                }
+                const int pp = s * C::NPS + (y + 2) * C::PP + (x + 2);
+                *reinterpret_cast<uint4 *>(sI + ch * C::PLANE_I + pp * 16) = v;
+            }
+            tc::fence_async_smem();
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
+        }
+    } else if (lane == 0) {
+        // ------------------------------ MMA issuer ------------------------------
+        const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
+        uint32_t acc = 0;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b = c & 1;
+            tc::mbar_wait(&bars[b], (uint32_t)((c >> 1) & 1));
+            tc::fence_after_sync();
+            const uint32_t d_base = tc::smem_u32(smem + b * C::BUF);
+            const uint32_t i_base = d_base + 8 * C::PLANE_D;
+#pragma unroll 1
+            for (int j = 0; j < C::KPIX / 16; ++j) {
+                const uint64_t ad = tc::smem_desc(d_base + (uint32_t)j * 256, 128, C::PLANE_D);
+#pragma unroll 1
+                for (int ti = 0; ti < ntap; ++ti) {
+                    const int tap = tap0 + ti, ky = tap / 5, kx = tap - ky * 5;
+                    const uint64_t bd = tc::smem_desc(i_base + (uint32_t)(j * 16 + ky * C::PP + kx) * 16, 128,
+                                                      C::PLANE_I);
+                    tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bd, idesc, acc);
+                }
+                acc = 1;
+            }
+            tc::mma_commit(&bars[2 + b]);          // buffer b may be refilled once these MMAs are done
+        }
+        tc::mma_commit(&bars[4]);
+    }
+    __syncwarp();
+    // ------------------------------ epilogue: TMEM -> gradient row ------------------------------
+    if (warp < 4) {
+        tc::mbar_wait(&bars[4], 0);
+        tc::fence_after_sync();
+        float *G = ws.G + (int64_t)g * ws.ldg + w_off;
+        // an M = 64 accumulator keeps rows 16q .. 16q+15 in lanes 0..15 of TMEM quadrant q
+        const int co = warp * 16 + lane;
+        for (int ti = 0; ti < ntap; ++ti) {
+            uint32_t r[32];
+            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ti * 32), r);
+            tc::tmem_ld_wait();
+            if (lane < 16 && co < COUT) {
+                float *dst = G + (co * 32) * 25 + (tap0 + ti);
+#pragma unroll
+                for (int ci = 0; ci < 32; ++ci) dst[ci * 25] = __uint_as_float(r[ci]);
+            }
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// bias gradient db[co] = sum over the group's samples and pixels of dY (fixed order: deterministic)
+template <int COUT, int H>
+__global__ void __launch_bounds__(256)
+conv_bias_grad_kernel(const float *__restrict__ dY, Pass p, Workspace ws, int b_off)
+{
+    __shared__ float part[256];
+    const int g = blockIdx.x, t = threadIdx.x;
+    if (p.gcount[g] <= 0) return;
+    constexpr int ROWS = 256 / COUT;                       // pixel lanes per channel
+    const int co = t % COUT, r = t / COUT;
+    float s = 0.f;
+    for (int sl = 0; sl < p.gs; ++sl) {
+        const int slot = g * p.gs + sl;
+        if (p.img_idx[slot] < 0) continue;
+        const float *src = dY + (int64_t)slot * (H * H * COUT);
+        for (int pix = r; pix < H * H; pix += ROWS) s += src[pix * COUT + co];
+    }
+    part[t] = s;
+    __syncthreads();
+    if (t < COUT) {
+        float tot = 0.f;
+        for (int k = 0; k < ROWS; ++k) tot += part[k * COUT + t];
+        ws.G[(int64_t)g * ws.ldg + b_off + t] = tot;
+    }
+}
+
+template <int COUT, int H, int SB>
+static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Workspace &ws, int w_off, int b_off,
+                           cudaStream_t st)
+{
+    using C = WgradTcCfg<COUT, H, SB>;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    conv_wgrad_tc_kernel<COUT, H, SB><<<p.n_groups * 2, WG_THREADS, C::SMEM, st>>>(in, dY, p, ws, w_off);
+    DLS_LAUNCH_CHECK();
+    conv_bias_grad_kernel<COUT, H><<<p.n_groups, 256, 0, st>>>(dY, p, ws, b_off);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_wgrad_tc<32, 15, 1>(ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2, st);
+}
+int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    return launch_wgrad_tc<64, 7, 4>(ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3, st);
+}
+
 }  // namespace gnl
 }  // namespace dls

@@ -44,7 +44,7 @@ def data():
     return imgs, labs
 
 
-WGRAD_TC = False     # set when the weight-gradient GEMMs also run on tensor cores
+WGRAD_TC = True      # set when the weight-gradient GEMMs also run on tensor cores
 TOL = {0: dict(logit=2e-4, grad_t=2e-4, grad_all=5e-5, par=1e-4, upd=2e-3, loss=1e-4, hits=1),
        1: dict(logit=6e-2, grad_t=1.5e-1, grad_all=1e-1, par=1e-3, upd=1.5e-1, loss=2e-2, hits=6)}
 

@@ -53,6 +53,44 @@ prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t 
     }
 }
 
+__device__ __forceinline__ uint4 pack_bf16x8(const float4 a, const float4 b) {
+    __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
+    __nv_bfloat162 q2 = __floats2bfloat162_rn(b.x, b.y), q3 = __floats2bfloat162_rn(b.z, b.w);
+    uint4 v;
+    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
+    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
+    return v;
+}
+
+// Staging loop with U independent 32-byte global loads in flight per thread (the copies are
+// latency bound otherwise).  `loc(i, src, dst)` maps item i to its fp32 source (nullptr = zeros) and
+// its 16-byte shared-memory destination.
+template <int U, typename Loc>
+__device__ __forceinline__ void stage_items(int first, int n_items, int stride, Loc loc) {
+    for (int base = first; base < n_items; base += U * stride) {
+        float4 a[U], b[U];
+        uint8_t *dst[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * stride;
+            dst[u] = nullptr;
+            a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            b[u] = a[u];
+            if (i < n_items) {
+                const float *src;
+                loc(i, src, dst[u]);
+                if (src) {
+                    a[u] = __ldg(reinterpret_cast<const float4 *>(src));
+                    b[u] = __ldg(reinterpret_cast<const float4 *>(src) + 1);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (dst[u]) *reinterpret_cast<uint4 *>(dst[u]) = pack_bf16x8(a[u], b[u]);
+    }
+}
+
 template <int CIN, int COUT, int H, int SB>
 struct ConvTcCfg {
     static constexpr int PP = H + 4;
@@ -110,24 +148,13 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
     __syncthreads();
-    for (int s = 0; s < n_s; ++s) {
+    stage_items<4>(t, n_s * H * H * C::NCH, 128, [&](int i, const float *&src, uint8_t *&dst) {
+        const int ch = i % C::NCH, q = i / C::NCH, s = q / (H * H), pix = q - s * (H * H);
+        const int y = pix / H, x = pix - y * H;
         const int slot = g * p.gs + s0 + s;
-        if (p.img_idx[slot] < 0) continue;
-        const float *src = in + (int64_t)slot * (H * H * CIN);
-        for (int i = t; i < H * H * C::NCH; i += 128) {
-            const int pix = i / C::NCH, ch = i - pix * C::NCH;
-            const int y = pix / H, x = pix - y * H;
-            const float4 a = *reinterpret_cast<const float4 *>(src + pix * CIN + ch * 8);
-            const float4 b = *reinterpret_cast<const float4 *>(src + pix * CIN + ch * 8 + 4);
-            __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
-            __nv_bfloat162 q2 = __floats2bfloat162_rn(b.x, b.y), q3 = __floats2bfloat162_rn(b.z, b.w);
-            uint4 v;
-            v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
-            v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
-            const int pp = s * C::NPS + (y + 2) * C::PP + (x + 2);
-            *reinterpret_cast<uint4 *>(sA + ch * C::PLANE + pp * 16) = v;
-        }
-    }
+        src = (p.img_idx[slot] >= 0) ? in + (int64_t)slot * (H * H * CIN) + pix * CIN + ch * 8 : nullptr;
+        dst = sA + ch * C::PLANE + (s * C::NPS + (y + 2) * C::PP + (x + 2)) * 16;
+    });
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -139,20 +166,20 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     const int n_origins = (n_s - 1) * C::NPS + C::LAST;
     const int n_tiles = (n_origins + 127) / 128;
 
+    // Descriptors differ between MMAs only in their 14-bit start-address field (address >> 4); all
+    // per-tap / per-K-step offsets are compile-time constants of the fully unrolled loops, so the
+    // single issuing thread spends two integer adds per MMA.
+    const uint64_t bd0 = tc::smem_desc(b_base, COUT * 16, 128);
     auto issue = [&](int tile) {
         const uint32_t d = tmem + (uint32_t)((tile & 1) * COUT);
-        uint32_t acc = 0;
-#pragma unroll 1
+        const uint64_t ad_tile = tc::smem_desc(a_base + (uint32_t)tile * 2048u, C::PLANE, 128);
+#pragma unroll
         for (int tap = 0; tap < 25; ++tap) {
-            const int ky = tap / 5, kx = tap - ky * 5;
-            const uint32_t a_tap = a_base + (uint32_t)(tile * 128 + ky * C::PP + kx) * 16;
 #pragma unroll
             for (int h = 0; h < CIN / 16; ++h) {
-                const uint64_t ad = tc::smem_desc(a_tap + (uint32_t)(2 * h) * C::PLANE, C::PLANE, 128);
-                const uint64_t bd = tc::smem_desc(b_base + (uint32_t)(tap * C::NCH + 2 * h) * (COUT * 16),
-                                                  COUT * 16, 128);
-                tc::mma_f16(d, ad, bd, idesc, acc);
-                acc = 1;
+                const uint64_t ad = ad_tile + (uint64_t)((((tap / 5) * C::PP + (tap % 5)) * 16 + 2 * h * C::PLANE) >> 4);
+                const uint64_t bd = bd0 + (uint64_t)(((tap * C::NCH + 2 * h) * (COUT * 16)) >> 4);
+                tc::mma_f16(d, ad, bd, idesc, (tap | h) != 0 ? 1u : 0u);
             }
         }
         tc::mma_commit(&bars[tile & 1]);
@@ -316,39 +343,22 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));   // MMAs of chunk c-2 done
             uint8_t *sD = smem + b * C::BUF;
             uint8_t *sI = sD + 8 * C::PLANE_D;
-            for (int i = pt; i < SB * C::NPS * (COUT / 8); i += WG_PRODUCERS) {
+            stage_items<4>(pt, SB * C::NPS * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
                 const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
                 const int sl = c * SB + s;
-                uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                if (sl < gs && oy < H && ox < H && p.img_idx[g * gs + sl] >= 0) {
-                    const float *src = dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8;
-                    const float4 a = *reinterpret_cast<const float4 *>(src);
-                    const float4 bb = *reinterpret_cast<const float4 *>(src + 4);
-                    __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
-                    __nv_bfloat162 q2 = __floats2bfloat162_rn(bb.x, bb.y), q3 = __floats2bfloat162_rn(bb.z, bb.w);
-                    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
-                    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
-                }
-                *reinterpret_cast<uint4 *>(sD + ch * C::PLANE_D + pix * 16) = v;
-            }
-            for (int i = pt; i < SB * H * H * 4; i += WG_PRODUCERS) {
+                const bool ok = sl < gs && oy < H && ox < H && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
+                src = ok ? dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8 : nullptr;
+                dst = sD + ch * C::PLANE_D + pix * 16;
+            });
+            stage_items<4>(pt, SB * H * H * 4, WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
                 const int y = pix / H, x = pix - y * H;
                 const int sl = c * SB + s;
-                uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                if (sl < gs && p.img_idx[g * gs + sl] >= 0) {
-                    const float *src = in + (int64_t)(g * gs + sl) * (H * H * 32) + pix * 32 + ch * 8;
-                    const float4 a = *reinterpret_cast<const float4 *>(src);
-                    const float4 bb = *reinterpret_cast<const float4 *>(src + 4);
-                    __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
-                    __nv_bfloat162 q2 = __floats2bfloat162_rn(bb.x, bb.y), q3 = __floats2bfloat162_rn(bb.z, bb.w);
-                    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
-                    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
-                }
-                const int pp = s * C::NPS + (y + 2) * C::PP + (x + 2);
-                *reinterpret_cast<uint4 *>(sI + ch * C::PLANE_I + pp * 16) = v;
-            }
+                const bool ok = sl < gs && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
+                src = ok ? in + (int64_t)(g * gs + sl) * (H * H * 32) + pix * 32 + ch * 8 : nullptr;
+                dst = sI + ch * C::PLANE_I + (s * C::NPS + (y + 2) * C::PP + (x + 2)) * 16;
+            });
             tc::fence_async_smem();
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
         }
@@ -356,22 +366,26 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         // ------------------------------ MMA issuer ------------------------------
         const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
         uint32_t acc = 0;
+        uint32_t tshift[C::TAPS0];                   // tap shift in 16-byte units (registers: loops are unrolled)
+#pragma unroll
+        for (int ti = 0; ti < C::TAPS0; ++ti) {
+            const int tap = tap0 + (ti < ntap ? ti : 0);
+            tshift[ti] = (uint32_t)((tap / 5) * C::PP + (tap % 5));
+        }
         for (int c = 0; c < n_chunks; ++c) {
             const int b = c & 1;
             tc::mbar_wait(&bars[b], (uint32_t)((c >> 1) & 1));
             tc::fence_after_sync();
             const uint32_t d_base = tc::smem_u32(smem + b * C::BUF);
-            const uint32_t i_base = d_base + 8 * C::PLANE_D;
+            const uint64_t ad0 = tc::smem_desc(d_base, 128, C::PLANE_D);
+            const uint64_t bd0 = tc::smem_desc(d_base + 8 * C::PLANE_D, 128, C::PLANE_I);
 #pragma unroll 1
             for (int j = 0; j < C::KPIX / 16; ++j) {
-                const uint64_t ad = tc::smem_desc(d_base + (uint32_t)j * 256, 128, C::PLANE_D);
-#pragma unroll 1
-                for (int ti = 0; ti < ntap; ++ti) {
-                    const int tap = tap0 + ti, ky = tap / 5, kx = tap - ky * 5;
-                    const uint64_t bd = tc::smem_desc(i_base + (uint32_t)(j * 16 + ky * C::PP + kx) * 16, 128,
-                                                      C::PLANE_I);
-                    tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bd, idesc, acc);
-                }
+                const uint64_t ad = ad0 + (uint64_t)(j * 16);
+                const uint64_t bdj = bd0 + (uint64_t)(j * 16);
+#pragma unroll
+                for (int ti = 0; ti < C::TAPS0; ++ti)
+                    if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
                 acc = 1;
             }
             tc::mma_commit(&bars[2 + b]);          // buffer b may be refilled once these MMAs are done

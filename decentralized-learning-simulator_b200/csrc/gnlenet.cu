@@ -750,8 +750,12 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     if (rc) return rc;
     const int S = p.n_groups * p.gs;
     const int sv = save ? 1 : 0;
-    conv1_pool_gn_relu_kernel<<<S, 256, K1_SMEM_BYTES, st>>>(p, ws, sv);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv1_fwd_tc(p, ws, save, st))) return rc;
+    } else {
+        conv1_pool_gn_relu_kernel<<<S, 256, K1_SMEM_BYTES, st>>>(p, ws, sv);
+        DLS_LAUNCH_CHECK();
+    }
     if (ws.precision == 1) {
         if ((rc = conv2_fwd_tc(p, ws, st))) return rc;
     } else {
@@ -823,8 +827,12 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     gn_block_bwd_kernel<32, 15, 15, false><<<S, 256, 0, st>>>(ws.da1, ws.a1, nullptr, ws.p1, ws.st1, ws.dp1,
                                                              ws.gnp, p, OFF_G1W, 0);
     DLS_LAUNCH_CHECK();
-    conv1_wgrad_kernel<<<dim3(p.n_groups, 4), 256, 0, st>>>(p, ws);
-    DLS_LAUNCH_CHECK();
+    if (ws.precision == 1) {
+        if ((rc = conv1_wgrad_tc(p, ws, st))) return rc;
+    } else {
+        conv1_wgrad_kernel<<<dim3(p.n_groups, 4), 256, 0, st>>>(p, ws);
+        DLS_LAUNCH_CHECK();
+    }
     gn_param_reduce_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     return 0;

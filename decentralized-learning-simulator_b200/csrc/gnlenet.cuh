@@ -28,7 +28,7 @@ constexpr int A3_SZ = PH3 * PH3 * C3;   // 576
 constexpr int GNP_SZ = 2 * (C1 + C2 + C3);   // per-slot partial GN parameter gradients (256)
 
 constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
-constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)
+constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200 + 2560;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)
 constexpr int PREP_SZ = 2 * W2T_SZ + 2 * W3T_SZ;   // W2t, W2d, W3t, W3d per model
 
 // All activations are NHWC fp32, one contiguous record per sample slot.
@@ -77,6 +77,9 @@ int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int prep_w1_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st);
+int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 
 int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);

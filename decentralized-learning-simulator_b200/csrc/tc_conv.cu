@@ -30,7 +30,7 @@ prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t 
     if (model_active && model_active[m] == 0) return;
     const float *row = p.X + (int64_t)p.mrow[m] * p.ldx;
     __nv_bfloat16 *dst = prep + (int64_t)m * TC_PREP_ELEMS;
-    const int total = backward ? TC_PREP_ELEMS : TCO_W3UD;
+    const int total = backward ? (TCO_W3UD + 51200) : TCO_W3UD;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         float v;
         if (i < TCO_W2UD) {                       // W2u: k = tap*32 + ci ; [k/8][n=co][k%8]
@@ -250,7 +250,7 @@ int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st
     prep_weights_tc_kernel<<<grid, 256, 0, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
                                                  active);
     DLS_LAUNCH_CHECK();
-    return 0;
+    return prep_w1_tc(p, ws, st);
 }
 
 int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)

@@ -1,0 +1,379 @@
+// conv1 (3 -> 32, 5x5, pad 2, 32x32 images) on tensor cores, fused with maxpool 3/2 + GroupNorm +
+// ReLU (block 1 of GNLeNet, dasklearn/models/cifar10.py:120-123), and its weight gradient.
+//
+// K = 75 is too thin for a channel-plane layout (3 channels), so the image is "x-expanded" in
+// shared memory: E[py][ox][16] = the 15 values (kx, c) of padded row py that output column ox needs
+// (+1 zero), as two 8-element planes.  For a fixed kernel row ky the A operand of 128 consecutive
+// output pixels (4 image rows) is then the plane shifted by ky*32 entries: 5 MMAs (M=128, N=32,
+// K=16) per tile, 8 tiles per image, no wasted rows.
+#include "gnlenet.cuh"
+#include "tc_common.cuh"
+#include <cuda_bf16.h>
+
+namespace dls {
+namespace gnl {
+
+constexpr int E_NP = 36 * 32;                 // entries per plane (py, ox)
+constexpr int E_PLANE = E_NP * 16;            // bytes
+constexpr int C1_W_BYTES = 10 * 32 * 16;      // W1u: [ky*2 + j][co][8] bf16
+constexpr int TCO_W1U = 153600;               // offset inside the per-model bf16 prep block (after conv2/3)
+
+// W1u[kc = ky*2+j][n = co][e] = W1[co][c][ky][kx] with 8j+e = kx*3+c (< 15), else 0
+__global__ void __launch_bounds__(256)
+prep_w1_tc_kernel(Pass p, __nv_bfloat16 *prep, const int32_t *model_active)
+{
+    const int m = blockIdx.x;
+    if (model_active && model_active[m] == 0) return;
+    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx;
+    __nv_bfloat16 *dst = prep + (int64_t)m * TC_PREP_ELEMS + TCO_W1U;
+    for (int i = threadIdx.x; i < 2560; i += 256) {
+        const int e = i & 7, n = (i >> 3) & 31, kc = i >> 8, ky = kc >> 1, j = kc & 1;
+        const int q = 8 * j + e;
+        float v = 0.f;
+        if (q < 15) { const int kx = q / 3, c = q - kx * 3; v = row[OFF_W1 + n * 75 + c * 25 + ky * 5 + kx]; }
+        dst[i] = __float2bfloat16_rn(v);
+    }
+}
+
+// Build the x-expanded bf16 planes of one image from its raw uint8 HWC bytes (in shared memory).
+__device__ __forceinline__ void build_expanded(const uint8_t *simg, const __nv_bfloat16 *lut, uint8_t *sE, int t,
+                                               int nthreads)
+{
+    for (int i = t; i < 36 * 32 * 2; i += nthreads) {
+        const int j = i & 1, ox = (i >> 1) & 31, py = i >> 6;
+        const int y = py - 2;
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        if (y >= 0 && y < 32) {
+            const int b0 = (ox - 2) * 3 + 8 * j;
+            const uint8_t *rowp = simg + y * 96;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int bi = b0 + e;
+                unsigned short h = 0;
+                if (bi >= 0 && bi < 96 && 8 * j + e < 15) h = __bfloat16_as_ushort(lut[rowp[bi]]);
+                w[e >> 1] |= (uint32_t)h << ((e & 1) * 16);
+            }
+        }
+        *reinterpret_cast<uint4 *>(sE + j * E_PLANE + (py * 32 + ox) * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+constexpr int C1F_SMEM = 2 * E_PLANE + C1_W_BYTES + 32 * 256 * 4 + 32 * 225 * 4 + 3072 + 512 + 32 * 4 + 32 * 4 + 64;
+
+__global__ void __launch_bounds__(128, 2)
+conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *sE = smem;
+    uint8_t *sW = sE + 2 * E_PLANE;
+    float *ring = reinterpret_cast<float *>(sW + C1_W_BYTES);        // [32 co][8 rows][32 ox]
+    float *ps = ring + 32 * 256;                                      // [32 co][225]
+    uint8_t *simg = reinterpret_cast<uint8_t *>(ps + 32 * 225);
+    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
+    float *sbias = reinterpret_cast<float *>(simg + 3072 + 512);
+    float *red = sbias + 32;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(red + 32);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+
+    const int slot = blockIdx.x, t = threadIdx.x, warp = t >> 5;
+    const int id = p.img_idx[slot];
+    if (id < 0) return;
+    const int g = slot / p.gs;
+    int m;
+    const float *row = model_row(p, g, m);
+
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
+        for (int i = t; i < IMG_BYTES / 16; i += 128) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
+        const uint4 *wsrc = reinterpret_cast<const uint4 *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
+                                                             (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
+        for (int i = t; i < C1_W_BYTES / 16; i += 128) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
+        for (int i = t; i < 256; i += 128) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
+        if (t < 32) sbias[t] = row[OFF_B1 + t];
+    }
+    if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 64);
+    __syncthreads();
+    build_expanded(simg, lut, sE, t, 128);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t idesc = tc::instr_desc_bf16(128, 32, 0, 0);
+    const uint64_t ad0 = tc::smem_desc(tc::smem_u32(sE), E_PLANE, 128);
+    const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sW), 32 * 16, 128);
+    auto issue = [&](int k) {
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+            tc::mma_f16(tmem + (uint32_t)((k & 1) * 32), ad0 + (uint64_t)(k * 128 + ky * 32),
+                        bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
+        tc::mma_commit(&bars[k & 1]);
+    };
+    if (t == 0) { issue(0); issue(1); }
+
+    uint8_t *idx_out = ws.idx1 ? ws.idx1 + (int64_t)slot * A1_SZ : nullptr;
+    for (int k = 0; k < 8; ++k) {
+        tc::mbar_wait(&bars[k & 1], (uint32_t)((k >> 1) & 1));
+        tc::fence_after_sync();
+        {
+            uint32_t r[32];
+            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((k & 1) * 32), r);
+            tc::tmem_ld_wait();
+            // thread t holds conv output pixel (row 4k + t/32, ox = t%32), 32 channels
+            const int rr = ((4 * k + (t >> 5)) & 7) * 32 + (t & 31);
+#pragma unroll
+            for (int co = 0; co < 32; ++co) ring[co * 256 + rr] = __uint_as_float(r[co]) + sbias[co];
+        }
+        tc::fence_before_sync();
+        __syncthreads();
+        tc::fence_after_sync();
+        if (t == 0 && k + 2 < 8) issue(k + 2);
+        // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins)
+        const int py_lo = (k == 0) ? 0 : 2 * k - 1, n_py = (k == 0) ? 1 : 2;
+        for (int o = t; o < n_py * 15 * 32; o += 128) {
+            const int co = o / (n_py * 15), q = o - co * (n_py * 15), py = py_lo + q / 15, px = q % 15;
+            float best = -INFINITY;
+            int bi = 0;
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 3; ++dx) {
+                    const float v = ring[co * 256 + ((2 * py + dy) & 7) * 32 + 2 * px + dx];
+                    if (v > best) { best = v; bi = dy * 3 + dx; }
+                }
+            const int pp = py * 15 + px;
+            ps[co * 225 + pp] = best;
+            if (save_bwd) idx_out[pp * 32 + co] = (uint8_t)bi;
+        }
+        __syncthreads();
+    }
+    if (warp == 0) tc::tmem_dealloc(tmem, 64);
+
+    // GroupNorm(2, 32) over 16 channels x 225 pixels per group, then ReLU (ps is channel-major)
+    float s0 = 0.f, s1 = 0.f;
+    for (int e = t; e < A1_SZ; e += 128) { const float v = ps[e]; if (e < 3600) s0 += v; else s1 += v; }
+    const float sum0 = block_sum(s0, red), sum1 = block_sum(s1, red);
+    const float inv_n = 1.f / 3600.f;
+    const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
+    float q0 = 0.f, q1 = 0.f;
+    for (int e = t; e < A1_SZ; e += 128) {
+        const float d = ps[e] - (e < 3600 ? mean0 : mean1);
+        if (e < 3600) q0 = fmaf(d, d, q0); else q1 = fmaf(d, d, q1);
+    }
+    const float v0 = block_sum(q0, red), v1 = block_sum(q1, red);
+    const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
+    float *a1 = ws.a1 + (int64_t)slot * A1_SZ;
+    float *p1 = save_bwd ? ws.p1 + (int64_t)slot * A1_SZ : nullptr;
+    const int co = t & 31;
+    const float gam = row[OFF_G1W + co], bet = row[OFF_G1B + co];
+    const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
+    for (int i = t; i < A1_SZ; i += 128) {                  // i = pp*32 + co (128 % 32 == 0: co fixed per thread)
+        const float x = ps[co * 225 + (i >> 5)];
+        const float v = (x - mean) * rstd * gam + bet;
+        a1[i] = v > 0.f ? v : 0.f;
+        if (save_bwd) p1[i] = x;
+    }
+    if (save_bwd && t == 0) {
+        float *st = ws.st1 + (int64_t)slot * 4;
+        st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv1 weight gradient on tensor cores.
+//   dW1[co][c][ky][kx] = sum over samples and conv-output positions o of dc1[o][co] * P[o + (ky,kx)][c]
+// where dc1 is the gradient w.r.t. the conv1 output: the pooled gradient dp1 routed to the arg-max
+// position of every 3x3/2 window (overlapping windows add up).  Reduction (K) = the 1024 positions
+// of an image; A = the x-expanded image E (MN-major: M = (ky, 8 taps-channels), eight ky "chunks"
+// 32 entries apart, of which ky >= 5 are don't-care rows), B = dc1 as dense bf16 channel planes.
+// One CTA per node; warps 1-7 stage sample s+1 (expand image, scatter dp1) while warp 0 issues the
+// 128 MMAs (M=64, N=32, K=16) of sample s.
+// ------------------------------------------------------------------------------------------
+constexpr int DC_PLANE = 1024 * 16;
+constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
+constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128;
+constexpr int C1W_THREADS = 256, C1W_PRODUCERS = 224;
+
+__device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 224;" ::: "memory"); }
+
+__global__ void __launch_bounds__(C1W_THREADS, 1)
+conv1_wgrad_tc_kernel(Pass p, Workspace ws)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *simg = smem + 2 * C1W_BUF;
+    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 3072 + 512);       // full[2], empty[2], done
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int g = blockIdx.x, gs = p.gs;
+    if (p.gcount[g] <= 0) return;
+    {
+        uint4 *z = reinterpret_cast<uint4 *>(smem);
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = t; i < 2 * C1W_BUF / 16; i += C1W_THREADS) z[i] = zero;
+        for (int i = t; i < 256; i += C1W_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
+    }
+    if (t == 0) {
+        tc::mbar_init(&bars[0], C1W_PRODUCERS); tc::mbar_init(&bars[1], C1W_PRODUCERS);
+        tc::mbar_init(&bars[2], 1); tc::mbar_init(&bars[3], 1); tc::mbar_init(&bars[4], 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 64);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp >= 1) {
+        const int pt = t - 32;
+        for (int s = 0; s < gs; ++s) {
+            const int b = s & 1, slot = g * gs + s;
+            const int id = p.img_idx[slot];
+            if (s >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((s >> 1) - 1) & 1));
+            uint8_t *sE = smem + b * C1W_BUF;
+            uint8_t *sD = sE + 2 * E_PLANE;
+            {
+                uint4 *z = reinterpret_cast<uint4 *>(sD);
+                const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+                for (int i = pt; i < 4 * DC_PLANE / 16; i += C1W_PRODUCERS) z[i] = zero;
+                if (id >= 0) {
+                    const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
+                    for (int i = pt; i < IMG_BYTES / 16; i += C1W_PRODUCERS)
+                        reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
+                }
+            }
+            producer_sync();
+            if (id >= 0) {
+                build_expanded(simg, lut, sE, pt, C1W_PRODUCERS);
+                const float *dp = ws.dp1 + (int64_t)slot * A1_SZ;
+                const uint8_t *ix = ws.idx1 + (int64_t)slot * A1_SZ;
+                // windows of one colour (py%2, px%2) never touch the same conv position, so the
+                // read-modify-write below is race free within a pass and the sum order is fixed
+                for (int colour = 0; colour < 4; ++colour) {
+                    const int cy = colour >> 1, cx = colour & 1;
+                    const int ny = (15 - cy + 1) / 2, nx = (15 - cx + 1) / 2;
+                    for (int i = pt; i < ny * nx * 32; i += C1W_PRODUCERS) {
+                        const int co = i & 31, w = i >> 5, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
+                        const int pp = py * 15 + px;
+                        const float d = dp[pp * 32 + co];
+                        const int ii = ix[pp * 32 + co];
+                        const int o = (2 * py + ii / 3) * 32 + 2 * px + ii % 3;
+                        __nv_bfloat16 *cell = reinterpret_cast<__nv_bfloat16 *>(sD + (co >> 3) * DC_PLANE + o * 16) + (co & 7);
+                        *cell = __float2bfloat16_rn(__bfloat162float(*cell) + d);
+                    }
+                    producer_sync();
+                }
+            }
+            tc::fence_async_smem();
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
+        }
+    } else if (lane == 0) {
+        const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
+        uint32_t acc = 0;
+        for (int s = 0; s < gs; ++s) {
+            const int b = s & 1;
+            tc::mbar_wait(&bars[b], (uint32_t)((s >> 1) & 1));
+            tc::fence_after_sync();
+            const uint32_t e_base = tc::smem_u32(smem + b * C1W_BUF);
+            const uint64_t ad0 = tc::smem_desc(e_base, 128, 512);                       // M chunks = ky, 32 entries apart
+            const uint64_t ad1 = tc::smem_desc(e_base + E_PLANE, 128, 512);
+            const uint64_t bd0 = tc::smem_desc(e_base + 2 * E_PLANE, 128, DC_PLANE);
+#pragma unroll 4
+            for (int j = 0; j < 64; ++j) {
+                tc::mma_f16(tmem, ad0 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
+                tc::mma_f16(tmem + 32, ad1 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
+                acc = 1;
+            }
+            tc::mma_commit(&bars[2 + b]);
+        }
+        tc::mma_commit(&bars[4]);
+    }
+    __syncwarp();
+    if (warp < 4) {
+        tc::mbar_wait(&bars[4], 0);
+        tc::fence_after_sync();
+        float *G = ws.G + (int64_t)g * ws.ldg + OFF_W1;
+        const int mrow = warp * 16 + lane;                 // valid for lane < 16: row (ky, e) of the M = 64 tile
+        const int ky = mrow >> 3, e = mrow & 7;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            uint32_t r[32];
+            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(j * 32), r);
+            tc::tmem_ld_wait();
+            const int q = 8 * j + e;
+            if (lane < 16 && ky < 5 && q < 15) {
+                const int kx = q / 3, c = q - kx * 3;
+#pragma unroll
+                for (int co = 0; co < 32; ++co) G[co * 75 + c * 25 + ky * 5 + kx] = __uint_as_float(r[co]);
+            }
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 64);
+}
+
+// bias gradient of conv1 = sum of the pooled gradient dp1 over samples and pixels (fixed order)
+__global__ void __launch_bounds__(256)
+conv1_bias_grad_kernel(Pass p, Workspace ws)
+{
+    __shared__ float part[256];
+    const int g = blockIdx.x, t = threadIdx.x, co = t & 31, r = t >> 5;
+    if (p.gcount[g] <= 0) return;
+    float s = 0.f;
+    for (int sl = 0; sl < p.gs; ++sl) {
+        const int slot = g * p.gs + sl;
+        if (p.img_idx[slot] < 0) continue;
+        const float *src = ws.dp1 + (int64_t)slot * A1_SZ;
+        for (int pix = r; pix < 225; pix += 8) s += src[pix * 32 + co];
+    }
+    part[t] = s;
+    __syncthreads();
+    if (t < 32) {
+        float tot = 0.f;
+        for (int k = 0; k < 8; ++k) tot += part[k * 32 + t];
+        ws.G[(int64_t)g * ws.ldg + OFF_B1 + t] = tot;
+    }
+}
+
+int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             C1W_SMEM);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    conv1_wgrad_tc_kernel<<<p.n_groups, C1W_THREADS, C1W_SMEM, st>>>(p, ws);
+    DLS_LAUNCH_CHECK();
+    conv1_bias_grad_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+int prep_w1_tc(const Pass &p, Workspace &ws, cudaStream_t st)
+{
+    const int32_t *active = p.gmodel ? nullptr : p.gcount;
+    prep_w1_tc_kernel<<<p.n_models, 256, 0, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), active);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
+{
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1F_SMEM);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    conv1_tc_kernel<<<p.n_groups * p.gs, 128, C1F_SMEM, st>>>(p, ws, save ? 1 : 0);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace gnl
+}  // namespace dls

@@ -124,7 +124,7 @@ class _ConvBf16(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
-        dx = torch.nn.grad.conv2d_input(x.shape, bf16r(w), bf16r(dy), padding=2)
+        dx = torch.nn.grad.conv2d_input(x.shape, bf16r(w), bf16r(dy), padding=2) if ctx.needs_input_grad[0] else None
         if ctx.wgrad_bf16:
             dw = torch.nn.grad.conv2d_weight(bf16r(x), w.shape, bf16r(dy), padding=2)
         else:
@@ -132,10 +132,10 @@ class _ConvBf16(torch.autograd.Function):
         return dx, dw, dy.sum(dim=(0, 2, 3)), None
 
 
-def gnlenet_forward_bf16(p, x, wgrad_bf16=False):
-    """GNLeNet with conv2/conv3 evaluated like the precision-1 kernels (conv1, GroupNorm, pooling,
-    classifier stay fp32).  Used to separate implementation errors from bf16 rounding effects."""
-    x = F.conv2d(x, p["features.0.weight"], p["features.0.bias"], padding=2)
+def gnlenet_forward_bf16(p, x, wgrad_bf16=False, conv1_wgrad_bf16=False):
+    """GNLeNet with the three convolutions evaluated like the precision-1 kernels (GroupNorm,
+    pooling, classifier stay fp32).  Used to separate implementation errors from bf16 rounding."""
+    x = _ConvBf16.apply(x, p["features.0.weight"], p["features.0.bias"], conv1_wgrad_bf16)
     x = F.max_pool2d(x, 3, 2)
     x = F.relu(F.group_norm(x, 2, p["features.2.weight"], p["features.2.bias"], eps=1e-5))
     x = _ConvBf16.apply(x, p["features.4.weight"], p["features.4.bias"], wgrad_bf16)
@@ -227,13 +227,13 @@ def train_task(layout, row: np.ndarray, mom: Optional[np.ndarray], images_u8: np
 
 
 def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarray, emulate_bf16: bool = False,
-                wgrad_bf16: bool = False) -> Tuple[np.ndarray, float]:
+                wgrad_bf16: bool = False, conv1_wgrad_bf16: bool = False) -> Tuple[np.ndarray, float]:
     """Mean-loss gradient of one minibatch (used to check the backward kernels in isolation).
     `emulate_bf16`: evaluate conv2/conv3 with bf16-rounded operands like the precision-1 kernels."""
     P = layout.P
     wl = torch.from_numpy(np.array(row[:P], dtype=np.float32, copy=True)).requires_grad_(True)
     if emulate_bf16:
-        out = gnlenet_forward_bf16(_views(layout, wl), to_tensor(images_u8), wgrad_bf16)
+        out = gnlenet_forward_bf16(_views(layout, wl), to_tensor(images_u8), wgrad_bf16, conv1_wgrad_bf16)
     else:
         out = forward(layout, wl, to_tensor(images_u8))
     loss = loss_fn(layout, out, torch.from_numpy(labels.astype(np.int64)))

@@ -44,6 +44,7 @@ def data():
     return imgs, labs
 
 
+CONV1_WGRAD_TC = True
 WGRAD_TC = True      # set when the weight-gradient GEMMs also run on tensor cores
 TOL = {0: dict(logit=2e-4, grad_t=2e-4, grad_all=5e-5, par=1e-4, upd=2e-3, loss=1e-4, hits=1),
        1: dict(logit=6e-2, grad_t=1.5e-1, grad_all=1e-1, par=1e-3, upd=1.5e-1, loss=2e-2, hits=6)}
@@ -108,7 +109,8 @@ def test_gradient_vs_autograd(cuda, data, batch, counts, precision):
         if precision == 1:
             # against the oracle that rounds the conv2/conv3 operands to bf16 the same way, the kernels
             # must agree tightly: what is left above is rounding, not an implementation error
-            gemu, _ = O.gradient_of(L, X[t], flat_i[sel], flat_l[sel], emulate_bf16=True, wgrad_bf16=WGRAD_TC)
+            gemu, _ = O.gradient_of(L, X[t], flat_i[sel], flat_l[sel], emulate_bf16=True, wgrad_bf16=WGRAD_TC,
+                                    conv1_wgrad_bf16=CONV1_WGRAD_TC)
             errs = {key: rel(Gh[t, off:off + int(np.prod(shp))], gemu[off:off + int(np.prod(shp))])
                     for key, shp, off in L.entries}
             # (residual: values that sit next to a bf16 rounding boundary flip with fp32 noise)

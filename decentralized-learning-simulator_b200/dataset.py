@@ -55,15 +55,17 @@ class DeviceDataset:
         `count[step, task]`.  A task runs min(steps[t], ceil(n_i / batch)) steps; the last batch
         may be partial (dasklearn/model_trainer.py:99-102)."""
         T, S = len(peers), (max(steps) if len(steps) else 0)
-        idx = -np.ones((S, T, batch), dtype=np.int32)
-        cnt = np.zeros((S, T), dtype=np.int32)
-        for t, (peer, rnd) in enumerate(zip(peers, rounds)):
-            perm = self.permutation(self.seed, int(peer), int(rnd), self.n_i)
-            base = self.local_of[int(peer)] * self.n_i
-            for s in range(steps[t]):
-                c = perm[s * batch:(s + 1) * batch]
-                if len(c) == 0:
-                    break
-                idx[s, t, :len(c)] = c + base
-                cnt[s, t] = len(c)
+        base = np.array([self.local_of[int(q)] * self.n_i for q in peers], dtype=np.int64).reshape(T, 1)
+        if self.permutation is synthetic.minibatch_permutation:
+            perm = synthetic.minibatch_permutations(self.seed, peers, rounds, self.n_i)     # one argsort per wave
+        else:
+            perm = np.stack([self.permutation(self.seed, int(q), int(r), self.n_i) for q, r in zip(peers, rounds)]) \
+                if T else np.zeros((0, self.n_i), np.int32)
+        steps_a = np.asarray(steps, dtype=np.int64).reshape(T, 1)
+        m = min(self.n_i, S * batch)
+        padded = -np.ones((T, S * batch), dtype=np.int64)
+        padded[:, :m] = perm[:, :m] + base
+        padded[np.arange(S * batch).reshape(1, -1) >= steps_a * batch] = -1          # per-task local_steps
+        idx = np.ascontiguousarray(padded.reshape(T, S, batch).transpose(1, 0, 2)).astype(np.int32)
+        cnt = (idx >= 0).sum(axis=2).astype(np.int32)
         return idx, cnt

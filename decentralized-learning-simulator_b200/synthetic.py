@@ -42,11 +42,29 @@ def make_test_split(n_test: int, hw: int, c: int, num_classes: int, seed: int = 
     return img, labels
 
 
+def _mix64(x: np.ndarray) -> np.ndarray:
+    """splitmix64 finaliser (vectorised, wraps modulo 2^64)."""
+    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return x ^ (x >> np.uint64(31))
+
+
+def minibatch_permutations(seed: int, nodes: Sequence[int], rounds: Sequence[int], n_i: int) -> np.ndarray:
+    """`perm[t, :]` = the scripted sample order node `nodes[t]` sees in round `rounds[t]` (stand-in
+    for the `shuffle=True` permutation of `dasklearn/model_trainer.py:87`): samples sorted by a
+    counter-based hash of (seed, node, round, sample).  Platform independent and vectorised over
+    all tasks of a wave (one argsort), so the host can script thousands of nodes per round."""
+    with np.errstate(over="ignore"):
+        nodes = np.asarray(nodes, dtype=np.uint64).reshape(-1, 1)
+        rounds = np.asarray(rounds, dtype=np.uint64).reshape(-1, 1)
+        base = _mix64(np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15) + nodes * np.uint64(0xD1B54A32D192ED03)
+                      + rounds * np.uint64(0x8CB92BA72F3D8DD7) + np.uint64(0x632BE59BD9B4E019))
+        keys = _mix64(base + np.arange(n_i, dtype=np.uint64).reshape(1, -1) * np.uint64(0x9E3779B97F4A7C15))
+    return np.argsort(keys, axis=1, kind="stable").astype(np.int32)
+
+
 def minibatch_permutation(seed: int, node: int, round_nr: int, n_i: int) -> np.ndarray:
-    """The scripted sample order a node's DataLoader yields in `round_nr` (stand-in for the
-    `shuffle=True` permutation of `dasklearn/model_trainer.py:87`)."""
-    rs = np.random.RandomState((seed * 1000003 + node * 1009 + round_nr) % (2 ** 31 - 1))
-    return rs.permutation(n_i).astype(np.int32)
+    return minibatch_permutations(seed, [node], [round_nr], n_i)[0]
 
 
 def minibatch_index(seed: int, nodes: Sequence[int], rounds: Sequence[int], n_i: int, batch: int,
@@ -55,16 +73,12 @@ def minibatch_index(seed: int, nodes: Sequence[int], rounds: Sequence[int], n_i:
     `count[t, step]`.  Steps executed = min(local_steps, ceil(n_i / batch)) and the last batch may
     be partial, exactly like the reference loop (`dasklearn/model_trainer.py:99-102`)."""
     T = len(nodes)
-    idx = -np.ones((T, local_steps, batch), dtype=np.int32)
-    cnt = np.zeros((T, local_steps), dtype=np.int32)
-    for t, (node, rnd) in enumerate(zip(nodes, rounds)):
-        perm = minibatch_permutation(seed, node, rnd, n_i)
-        for s in range(local_steps):
-            chunk = perm[s * batch:(s + 1) * batch]
-            if len(chunk) == 0:
-                break
-            idx[t, s, :len(chunk)] = chunk
-            cnt[t, s] = len(chunk)
+    perm = minibatch_permutations(seed, nodes, rounds, n_i) if T else np.zeros((0, n_i), np.int32)
+    padded = -np.ones((T, local_steps * batch), dtype=np.int32)
+    m = min(n_i, local_steps * batch)
+    padded[:, :m] = perm[:, :m]
+    idx = padded.reshape(T, local_steps, batch)
+    cnt = (idx >= 0).sum(axis=2).astype(np.int32)
     return idx, cnt
 
 

@@ -8,6 +8,7 @@
 // All activations are NHWC fp32 records per sample slot in the caller's workspace.  Every
 // reduction uses a fixed order (no float atomics), so results are run-to-run deterministic.
 #include "gnlenet.cuh"
+#include "conv_simt.cuh"
 #include <math.h>
 
 namespace dls {
@@ -223,87 +224,6 @@ conv1_pool_gn_relu_kernel(Pass p, Workspace ws, int save_bwd)
         if (t == 0) {
             float *st = ws.st1 + (int64_t)slot * 4;
             st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// generic 5x5 / pad 2 convolution, NHWC, weights [tap][CIN][COUT]; one CTA per sample slot.
-// lane = output channel (COUT/32 per lane), warp = output rows {w, w+8}.  Used for conv2/conv3
-// forward and (with the transposed + flipped weight copies) for their data gradients.
-// ------------------------------------------------------------------------------------------
-template <int CIN, int COUT, int H, bool BIAS>
-__global__ void __launch_bounds__(256)
-conv5_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p, const float *prep,
-             int prep_off, int bias_off)
-{
-    constexpr int HP = H + 4;
-    constexpr int RPW = (H + 7) / 8;
-    constexpr int NCO = COUT / 32;
-    extern __shared__ __align__(16) float ins[];   // [HP][HP][CIN]
-    const int slot = blockIdx.x, t = threadIdx.x;
-    if (p.img_idx[slot] < 0) return;
-    const int g = slot / p.gs;
-    int m;
-    const float *row = model_row(p, g, m);
-    const float *wt = prep + (int64_t)m * PREP_STRIDE + prep_off;
-    const float *src = in + (int64_t)slot * (H * H * CIN);
-    for (int i = t; i < HP * HP * CIN; i += 256) {
-        const int c = i % CIN, pp = i / CIN, yy = pp / HP, xx = pp - yy * HP;
-        const bool inside = (yy >= 2) && (yy < H + 2) && (xx >= 2) && (xx < H + 2);
-        ins[i] = inside ? src[((yy - 2) * H + (xx - 2)) * CIN + c] : 0.f;
-    }
-    __syncthreads();
-
-    const int lane = t & 31, w = t >> 5;
-    float acc[RPW][H][NCO];
-#pragma unroll
-    for (int n = 0; n < NCO; ++n) {
-        const float b = BIAS ? row[bias_off + lane + 32 * n] : 0.f;
-#pragma unroll
-        for (int r = 0; r < RPW; ++r)
-#pragma unroll
-            for (int x = 0; x < H; ++x) acc[r][x][n] = b;
-    }
-    int yr[RPW];
-#pragma unroll
-    for (int r = 0; r < RPW; ++r) yr[r] = min(w + 8 * r, H - 1);
-
-    for (int ky = 0; ky < 5; ++ky) {
-#pragma unroll 2
-        for (int ci = 0; ci < CIN; ++ci) {
-            float rv[RPW][HP];
-#pragma unroll
-            for (int r = 0; r < RPW; ++r) {
-                const float *ip = ins + ((yr[r] + ky) * HP) * CIN + ci;
-#pragma unroll
-                for (int xx = 0; xx < HP; ++xx) rv[r][xx] = ip[xx * CIN];
-            }
-#pragma unroll
-            for (int kx = 0; kx < 5; ++kx) {
-                float wv[NCO];
-#pragma unroll
-                for (int n = 0; n < NCO; ++n)
-                    wv[n] = __ldg(wt + ((ky * 5 + kx) * CIN + ci) * COUT + lane + 32 * n);
-#pragma unroll
-                for (int r = 0; r < RPW; ++r)
-#pragma unroll
-                    for (int x = 0; x < H; ++x)
-#pragma unroll
-                        for (int n = 0; n < NCO; ++n)
-                            acc[r][x][n] = fmaf(rv[r][x + kx], wv[n], acc[r][x][n]);
-            }
-        }
-    }
-    float *dst = out + (int64_t)slot * (H * H * COUT);
-#pragma unroll
-    for (int r = 0; r < RPW; ++r) {
-        const int y = w + 8 * r;
-        if (y < H) {
-#pragma unroll
-            for (int x = 0; x < H; ++x)
-#pragma unroll
-                for (int n = 0; n < NCO; ++n) dst[(y * H + x) * COUT + lane + 32 * n] = acc[r][x][n];
         }
     }
 }
@@ -562,71 +482,6 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
 }
 
 // ------------------------------------------------------------------------------------------
-// weight gradient of a 5x5 convolution with CIN = 32: dW[co][ci][tap] = sum over the group's
-// samples and pixels of dY[pix][co] * in[pix shifted by tap][ci];  also the bias gradient.
-// grid = (n_groups, COUT/16); warp w owns output channels {2w, 2w+1} of the chunk, lane = ci.
-// Written straight into the gradient row in the reference's [co][ci][5][5] layout.
-// ------------------------------------------------------------------------------------------
-template <int COUT, int H>
-__global__ void __launch_bounds__(256)
-conv_wgrad_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws,
-                  int w_off, int b_off)
-{
-    constexpr int CIN = 32, HP = H + 4;
-    extern __shared__ __align__(16) float smw[];
-    float *ins = smw;                        // [HP][HP][32]
-    float *dys = smw + HP * HP * CIN;        // [H*H][16]
-    const int g = blockIdx.x, chunk = blockIdx.y, t = threadIdx.x, lane = t & 31, w = t >> 5;
-    if (p.gcount[g] <= 0) return;
-    for (int i = t; i < HP * HP * CIN; i += 256) ins[i] = 0.f;
-    float acc0[25], acc1[25];
-#pragma unroll
-    for (int k = 0; k < 25; ++k) { acc0[k] = 0.f; acc1[k] = 0.f; }
-    float bs0 = 0.f, bs1 = 0.f;
-    const int gs = p.gs;
-    for (int s = 0; s < gs; ++s) {
-        const int slot = g * gs + s;
-        if (p.img_idx[slot] < 0) continue;
-        __syncthreads();
-        const float *src = in + (int64_t)slot * (H * H * CIN);
-        for (int i = t; i < H * H * CIN; i += 256) {
-            const int c = i & 31, pix = i >> 5, y = pix / H, x = pix - y * H;
-            ins[((y + 2) * HP + x + 2) * CIN + c] = src[i];
-        }
-        const float *dsrc = dY + (int64_t)slot * (H * H * COUT) + chunk * 16;
-        for (int i = t; i < H * H * 16; i += 256) dys[i] = dsrc[(i >> 4) * COUT + (i & 15)];
-        __syncthreads();
-        int y = 0, x = 0;
-        for (int pix = 0; pix < H * H; ++pix) {
-            const float2 d = *reinterpret_cast<const float2 *>(dys + pix * 16 + 2 * w);
-            const float *ip = ins + (y * HP + x) * CIN + lane;
-#pragma unroll
-            for (int ky = 0; ky < 5; ++ky)
-#pragma unroll
-                for (int kx = 0; kx < 5; ++kx) {
-                    const float v = ip[(ky * HP + kx) * CIN];
-                    acc0[ky * 5 + kx] = fmaf(d.x, v, acc0[ky * 5 + kx]);
-                    acc1[ky * 5 + kx] = fmaf(d.y, v, acc1[ky * 5 + kx]);
-                }
-            if (++x == H) { x = 0; ++y; }
-        }
-        for (int pix = lane; pix < H * H; pix += 32) {
-            bs0 += dys[pix * 16 + 2 * w];
-            bs1 += dys[pix * 16 + 2 * w + 1];
-        }
-    }
-    float *G = ws.G + (int64_t)g * ws.ldg;
-    const int co0 = chunk * 16 + 2 * w;
-    float *g0 = G + w_off + (co0 * CIN + lane) * 25;
-    float *g1 = g0 + CIN * 25;
-#pragma unroll
-    for (int k = 0; k < 25; ++k) { g0[k] = acc0[k]; g1[k] = acc1[k]; }
-    bs0 = warp_sum(bs0);
-    bs1 = warp_sum(bs1);
-    if (lane == 0) { G[b_off + co0] = bs0; G[b_off + co0 + 1] = bs1; }
-}
-
-// ------------------------------------------------------------------------------------------
 // conv1 weight gradient.  The gradient w.r.t. the conv1 output is non-zero only at the arg-max
 // position of every pooling window, so dW1[co] = sum_p dp1[p][co] * patch(argmax(p, co)).
 // grid = (n_groups, 4); warp = output channel, lanes cover the 75 (ci,ky,kx) weights.
@@ -759,7 +614,7 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     if (ws.precision == 1) {
         if ((rc = conv2_fwd_tc(p, ws, st))) return rc;
     } else {
-        conv5_kernel<32, 32, 15, true><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PO_W2T, OFF_B2);
+        conv5_kernel<32, 32, 15, true><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PREP_STRIDE, PO_W2T, OFF_B2);
         DLS_LAUNCH_CHECK();
     }
     gn_pool_relu_kernel<32, 15, 7><<<S, 256, 0, st>>>(ws.c2, ws.a2, ws.st2, ws.idx2, p, OFF_G2W, OFF_G2B, sv);
@@ -767,7 +622,7 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     if (ws.precision == 1) {
         if ((rc = conv3_fwd_tc(p, ws, st))) return rc;
     } else {
-        conv5_kernel<32, 64, 7, true><<<S, 256, 11 * 11 * 32 * 4, st>>>(ws.a2, ws.c3, p, ws.prep, PO_W3T, OFF_B3);
+        conv5_kernel<32, 64, 7, true><<<S, 256, 11 * 11 * 32 * 4, st>>>(ws.a2, ws.c3, p, ws.prep, PREP_STRIDE, PO_W3T, OFF_B3);
         DLS_LAUNCH_CHECK();
     }
     gn_pool_relu_kernel<64, 7, 3><<<S, 256, 0, st>>>(ws.c3, ws.a3, ws.st3, ws.idx3, p, OFF_G3W, OFF_G3B, sv);
@@ -803,7 +658,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     if (ws.precision == 1) {
         if ((rc = conv3_dgrad_tc(p, ws, st))) return rc;
     } else {
-        conv5_kernel<64, 32, 7, false><<<S, 256, 11 * 11 * 64 * 4, st>>>(ws.dc3, ws.da2, p, ws.prep, PO_W3D, 0);
+        conv5_kernel<64, 32, 7, false><<<S, 256, 11 * 11 * 64 * 4, st>>>(ws.dc3, ws.da2, p, ws.prep, PREP_STRIDE, PO_W3D, 0);
         DLS_LAUNCH_CHECK();
     }
     // block 2
@@ -820,7 +675,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     if (ws.precision == 1) {
         if ((rc = conv2_dgrad_tc(p, ws, st))) return rc;
     } else {
-        conv5_kernel<32, 32, 15, false><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PO_W2D, 0);
+        conv5_kernel<32, 32, 15, false><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PREP_STRIDE, PO_W2D, 0);
         DLS_LAUNCH_CHECK();
     }
     // block 1 (GroupNorm -> ReLU after the pool), then the sparse conv1 weight gradient

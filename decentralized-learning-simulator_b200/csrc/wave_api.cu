@@ -2,6 +2,15 @@
 #include "gnlenet.cuh"
 
 namespace dls {
+namespace fem {
+int64_t train_workspace_bytes(int n_tasks, int batch, bool own_G);
+int step(const gnl::Pass &p, void *workspace, float *G, int64_t ldg, float *loss_out, float **G_used,
+         int64_t *ldg_used, cudaStream_t st);
+int64_t eval_workspace_bytes(int n_models, int n_test);
+int eval(const float *X, int64_t ldx, const int32_t *model_rows, int n_models, const uint8_t *test_images,
+         const int64_t *test_labels, int n_test, int32_t *out_correct, double *out_loss_sum, float *out_logits,
+         void *workspace, cudaStream_t st);
+}  // namespace fem
 
 // Fused optimizer update over the wave's rows — torch.optim.SGD semantics
 // (reference: dasklearn/optimizer/sgd.py:4-14; state carry-over dasklearn/model_trainer.py:89-92):
@@ -85,6 +94,7 @@ extern "C" int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int3
     if (n_tasks < 0 || batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
     // sized for either precision (the tensor-core path adds bf16 weight copies)
     if (arch == DLS_ARCH_GNLENET) return gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true, 1);
+    if (arch == DLS_ARCH_FEMNIST) return fem::train_workspace_bytes(n_tasks, batch, true);
     return DLS_E_SHAPE;
 }
 
@@ -106,8 +116,40 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
                               float *loss_out, int32_t precision, void *workspace,
                               int64_t workspace_bytes, void *stream)
 {
-    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (arch != DLS_ARCH_GNLENET && arch != DLS_ARCH_FEMNIST) return DLS_E_SHAPE;
     if (precision != 0 && precision != 1) return DLS_E_SHAPE;
+    if (arch == DLS_ARCH_FEMNIST) {
+        // FEMNIST CNN: fp32 CUDA-core kernels only (precision is ignored)
+        if (!task_row || !task_peer || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0 ||
+            n_steps < 0)
+            return DLS_E_ARG;
+        if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
+        int rcf = check_rows(X, ldx, DLS_FEMNIST_P);
+        if (rcf) return rcf;
+        if (mu != 0.f) {
+            if ((rcf = check_rows(M, ldm, DLS_FEMNIST_P))) return rcf;
+            if (!mom_first) return DLS_E_ARG;
+        }
+        if (n_tasks == 0 || n_steps == 0) return 0;
+        if (workspace_bytes < fem::train_workspace_bytes(n_tasks, batch, true)) return DLS_E_WS;
+        cudaStream_t stf = (cudaStream_t)stream;
+        for (int s = 0; s < n_steps; ++s) {
+            gnl::Pass p;
+            p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks; p.gmodel = nullptr; p.mrow = task_row;
+            p.img_idx = mb_index + (int64_t)s * n_tasks * batch; p.gcount = mb_count + (int64_t)s * n_tasks;
+            p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
+            float *G = nullptr;
+            int64_t ldg = 0;
+            if ((rcf = fem::step(p, workspace, nullptr, 0, loss_out ? loss_out + (int64_t)s * n_tasks : nullptr, &G,
+                                 &ldg, stf)))
+                return rcf;
+            dim3 grid(128, n_tasks);
+            sgd_update_kernel<<<grid, 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
+                                                     s == 0 ? mom_first : nullptr, p.gcount, DLS_FEMNIST_P, lr, mu, wd);
+            DLS_LAUNCH_CHECK();
+        }
+        return 0;
+    }
     if (!task_row || !task_peer || !images || !labels || !mb_index || !mb_count || !workspace ||
         n_tasks < 0 || n_steps < 0)
         return DLS_E_ARG;
@@ -145,8 +187,21 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
                              int32_t batch, float *loss_out, int32_t precision, void *workspace,
                              int64_t workspace_bytes, void *stream)
 {
-    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (arch != DLS_ARCH_GNLENET && arch != DLS_ARCH_FEMNIST) return DLS_E_SHAPE;
     if (precision != 0 && precision != 1) return DLS_E_SHAPE;
+    if (arch == DLS_ARCH_FEMNIST) {
+        if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0) return DLS_E_ARG;
+        if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
+        int rcf = check_rows(X, ldx, DLS_FEMNIST_P);
+        if (rcf) return rcf;
+        if ((rcf = check_rows(G, ldg, DLS_FEMNIST_P))) return rcf;
+        if (n_tasks == 0) return 0;
+        if (workspace_bytes < fem::train_workspace_bytes(n_tasks, batch, false)) return DLS_E_WS;
+        gnl::Pass p;
+        p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks; p.gmodel = nullptr; p.mrow = task_row;
+        p.img_idx = mb_index; p.gcount = mb_count; p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
+        return fem::step(p, workspace, G, ldg, loss_out, nullptr, nullptr, (cudaStream_t)stream);
+    }
     if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0)
         return DLS_E_ARG;
     if (batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
@@ -167,6 +222,7 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
 
 extern "C" int64_t dls_eval_workspace_bytes(int32_t arch, int32_t n_models, int32_t n_test)
 {
+    if (arch == DLS_ARCH_FEMNIST && n_models >= 0 && n_test >= 0) return fem::eval_workspace_bytes(n_models, n_test);
     if (arch != DLS_ARCH_GNLENET || n_models < 0 || n_test < 0) return DLS_E_SHAPE;
     const int gpm = (n_test + EVAL_GS - 1) / EVAL_GS;
     const int64_t total_groups = (int64_t)n_models * gpm;
@@ -181,8 +237,19 @@ extern "C" int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const in
                              float *out_logits, int32_t precision, void *workspace,
                              int64_t workspace_bytes, void *stream)
 {
-    if (arch != DLS_ARCH_GNLENET) return DLS_E_SHAPE;
+    if (arch != DLS_ARCH_GNLENET && arch != DLS_ARCH_FEMNIST) return DLS_E_SHAPE;
     if (precision != 0 && precision != 1) return DLS_E_SHAPE;
+    if (arch == DLS_ARCH_FEMNIST) {
+        if (!model_rows || !test_images || !test_labels || !out_correct || !out_loss_sum || !workspace ||
+            n_models < 0 || n_test < 0)
+            return DLS_E_ARG;
+        int rcf = check_rows(X, ldx, DLS_FEMNIST_P);
+        if (rcf) return rcf;
+        if (n_models == 0 || n_test == 0) return 0;
+        if (workspace_bytes < fem::eval_workspace_bytes(n_models, n_test)) return DLS_E_WS;
+        return fem::eval(X, ldx, model_rows, n_models, test_images, test_labels, n_test, out_correct, out_loss_sum,
+                         out_logits, workspace, (cudaStream_t)stream);
+    }
     if (!model_rows || !test_images || !test_labels || !out_correct || !out_loss_sum || !workspace ||
         n_models < 0 || n_test < 0)
         return DLS_E_ARG;

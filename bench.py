@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--precision", type=int, default=1,
                     help="1 = bf16 tcgen05 convolutions with fp32 accumulation (default), 0 = fp32 CUDA cores")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--model", default="gnlenet", choices=["gnlenet", "femnist"],
+                    help="gnlenet = BASELINE configs[1] (default); femnist = the C3 model (fp32 path)")
     return ap.parse_args()
 
 
@@ -206,13 +208,17 @@ def run_reference(args):
 
 
 def workload_config(n_nodes, k, args):
-    return {"workload": "D-PSGD round: %d nodes (%d per GPU), %d-regular topology, GNLeNet (P=%d), synthetic "
-                        "CIFAR-10-shaped uint8 data, n_i=%d, B=%d, local_steps=%d, lr 0.002, momentum 0.9"
-                        % (n_nodes, args.nodes_per_gpu, k, GNLENET_P, N_I, BATCH, LOCAL_STEPS),
+    return {"workload": "D-PSGD round: %d nodes (%d per GPU), %d-regular topology, %s (P=%d), synthetic "
+                        "%s uint8 data, n_i=%d, B=%d, local_steps=%d, %s"
+                        % (n_nodes, args.nodes_per_gpu, k, "GNLeNet" if args.model == "gnlenet" else "FEMNIST CNN",
+                           GNLENET_P, "CIFAR-10-shaped" if args.model == "gnlenet" else "FEMNIST-shaped 28x28",
+                           N_I, BATCH, LOCAL_STEPS,
+                           "lr 0.002, momentum 0.9" if args.model == "gnlenet" else "lr 0.004, momentum 0"),
             "nodes": n_nodes, "k": k, "batch": BATCH, "local_steps": LOCAL_STEPS,
             "l2": "inputs larger than L2: the train wave streams its ~1.9 GB activation workspace between "
                   "aggregate launches, so X/Y (87 MB) are not L2-resident when a wave starts",
-            "train_math": "fp32 CUDA cores" if args.precision == 0 else "bf16 tensor cores, fp32 accumulate",
+            "train_math": "fp32 CUDA cores" if (args.precision == 0 or args.model == "femnist")
+            else "bf16 tcgen05 tensor cores, fp32 accumulate",
             "dataset_residency": "node partitions uploaded once (like the reference's cached partitions); "
                                  "e2e uploads per-round task descriptors + minibatch index"}
 
@@ -229,9 +235,13 @@ def main():
     from dls_b200 import _lib, synthetic
     from dls_b200.dataset import DeviceDataset
     from dls_b200.executor import WaveExecutor
-    from dls_b200.layout import GNLENET as L
+    from dls_b200.layout import GNLENET, FEMNIST
     from dls_b200.settings import SessionSettings, LearningSettings
     from dls_b200.solver import BatchedSolver
+    L = GNLENET if args.model == "gnlenet" else FEMNIST
+    global GNLENET_P, GFLOP_PER_NODE_STEP
+    if args.model == "femnist":
+        GNLENET_P, GFLOP_PER_NODE_STEP = FEMNIST.P, 2.321
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
@@ -254,8 +264,14 @@ def main():
         k += 1
     W, Ksteps = args.warmup, args.steps
     rounds = W + Ksteps
-    st = SessionSettings(participants=n_nodes, seed=42, data_dir=os.path.join(REPO, "gpurun_out", "bench_data"),
-                         learning=LearningSettings(0.002, 0.9, 0.0, BATCH, LOCAL_STEPS), k=k, precision=args.precision)
+    if args.model == "femnist":      # reference defaults for femnist: lr 0.004, momentum 0 (args.py:70-72)
+        st = SessionSettings(participants=n_nodes, seed=42, dataset="femnist", model=None,
+                             data_dir=os.path.join(REPO, "gpurun_out", "bench_data"),
+                             learning=LearningSettings(0.004, 0.0, 0.0, BATCH, LOCAL_STEPS), k=k, precision=0)
+    else:
+        st = SessionSettings(participants=n_nodes, seed=42, data_dir=os.path.join(REPO, "gpurun_out", "bench_data"),
+                             learning=LearningSettings(0.002, 0.9, 0.0, BATCH, LOCAL_STEPS), k=k,
+                             precision=args.precision)
     nbrs = synthetic.kreg_topology(n_nodes, k, seed=42)
     if world > 1:
         from dls_b200.partition import DistributedSolver, partition_nodes
@@ -365,7 +381,7 @@ def main():
         line = {
             "metric": "node-train-steps/sec", "value": value, "unit": "node-train-steps/s", "n_gpus": world,
             "steps": Ksteps, "warmup": W, "ms_per_step": total_ms / Ksteps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == 0 else "bf16",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if (args.precision == 0 or args.model == "femnist") else "bf16",
             "data": "synthetic", "config": workload_config(n_nodes, k, args),
             "aggregate": {"metric": "gossip-aggregate HBM GB/s", "value": agg_gbs * world, "unit": "GB/s",
                           "ms_per_wave": agg_t, "bytes_per_wave_per_gpu": agg_bytes,

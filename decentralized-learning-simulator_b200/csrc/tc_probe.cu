@@ -9,7 +9,7 @@ namespace dls {
 __global__ void __launch_bounds__(128)
 tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *__restrict__ b_img, int b_bytes,
                 const uint64_t *__restrict__ a_desc, const uint64_t *__restrict__ b_desc, int n_mma,
-                uint32_t idesc, int ncols, float *__restrict__ out)
+                uint32_t idesc, int ncols, float *__restrict__ out, int repeat, long long *__restrict__ cycles_out)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar;
@@ -20,20 +20,30 @@ tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *_
     for (int i = t; i < a_bytes; i += 128) sa[i] = a_img[i];
     for (int i = t; i < b_bytes; i += 128) sb[i] = b_img[i];
     if (t == 0) { tc::mbar_init(&bar, 1); tc::mbar_fence_init(); }
-    if (warp == 0) tc::tmem_alloc(&tmem_base, 64);
+    if (warp == 0) tc::tmem_alloc(&tmem_base, 128);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tm = tmem_base;
+    long long t0 = 0;
     if (t == 0) {
         const uint32_t abase = tc::smem_u32(sa) >> 4, bbase = tc::smem_u32(sb) >> 4;
+        uint64_t ad[8], bd[8];
+        for (int i = 0; i < 8; ++i) { ad[i] = a_desc[i % n_mma] + abase; bd[i] = b_desc[i % n_mma] + bbase; }
         for (int i = 0; i < n_mma; ++i)
             tc::mma_f16(tm, a_desc[i] + abase, b_desc[i] + bbase, idesc, i > 0 ? 1u : 0u);
+        t0 = clock64();
+        // throughput probe: re-issue the first (up to 8) MMAs `repeat` times into spare columns
+        for (int r = 0; r < repeat; ++r) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) tc::mma_f16(tm + 64, ad[i], bd[i], idesc, 1u);
+        }
         tc::mma_commit(&bar);
     }
     tc::mbar_wait(&bar, 0);
     tc::fence_after_sync();
+    if (t == 0 && cycles_out) *cycles_out = clock64() - t0;
     uint32_t r[32];
     for (int c0 = 0; c0 < ncols; c0 += 32) {
         tc::tmem_ld32(tm + ((uint32_t)(warp * 32) << 16) + c0, r);
@@ -42,7 +52,7 @@ tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *_
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(tm, 64);
+    if (warp == 0) tc::tmem_dealloc(tm, 128);
 }
 
 }  // namespace dls
@@ -53,7 +63,7 @@ using namespace dls;
 // adds the image's shared-memory address); out: [128 TMEM lanes][ncols] floats, ncols <= 64.
 extern "C" int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, int32_t b_bytes,
                             const uint64_t *a_desc, const uint64_t *b_desc, int32_t n_mma, uint32_t idesc,
-                            int32_t ncols, float *out, void *stream)
+                            int32_t ncols, float *out, int32_t repeat, long long *cycles_out, void *stream)
 {
     if (!a_img || !b_img || !a_desc || !b_desc || !out || n_mma <= 0 || ncols <= 0 || ncols > 64) return DLS_E_ARG;
     const size_t smem = ((size_t)(a_bytes + 1023) & ~(size_t)1023) + (size_t)b_bytes + 1024;
@@ -61,7 +71,7 @@ extern "C" int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t
     cudaError_t e = cudaFuncSetAttribute(tc_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     tc_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(a_img, a_bytes, b_img, b_bytes, a_desc, b_desc, n_mma,
-                                                            idesc, ncols, out);
+                                                            idesc, ncols, out, repeat, cycles_out);
     DLS_LAUNCH_CHECK();
     return 0;
 }

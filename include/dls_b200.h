@@ -131,7 +131,8 @@ int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const int32_t *mode
  * No reference counterpart. */
 int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, int32_t b_bytes,
                  const uint64_t *a_desc, const uint64_t *b_desc, int32_t n_mma, uint32_t idesc,
-                 int32_t ncols, float *out, void *stream);
+                 int32_t ncols, float *out, int32_t repeat /* re-issue the first 8 MMAs this many times */,
+                 long long *cycles_out /* optional: SM cycles for the repeated MMAs */, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * test wave without a workspace argument.  This entry point has NO counterpart in the reference;

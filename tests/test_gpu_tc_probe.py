@@ -30,16 +30,20 @@ def idesc(M, N, a_mn, b_mn):
     return (1 << 4) | (1 << 7) | (1 << 10) | (a_mn << 15) | (b_mn << 16) | ((N >> 3) << 17) | ((M >> 4) << 24)
 
 
-def run(cuda, a_img, b_img, a_desc, b_desc, idsc, ncols):
+def run(cuda, a_img, b_img, a_desc, b_desc, idsc, ncols, repeat=0):
     out = torch.full((128, ncols), float("nan"), device=cuda)
+    cyc = torch.zeros(1, dtype=torch.int64, device=cuda)
     ta = torch.from_numpy(a_img.view(np.uint8)).to(cuda)
     tb = torch.from_numpy(b_img.view(np.uint8)).to(cuda)
     da = torch.from_numpy(np.array(a_desc, dtype=np.uint64).view(np.int64)).to(cuda)
     db = torch.from_numpy(np.array(b_desc, dtype=np.uint64).view(np.int64)).to(cuda)
     rc = _lib.lib().dls_tc_probe(ta.data_ptr(), ta.numel(), tb.data_ptr(), tb.numel(), da.data_ptr(), db.data_ptr(),
-                                 len(a_desc), idsc, ncols, out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+                                 len(a_desc), idsc, ncols, out.data_ptr(), repeat, cyc.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     torch.cuda.synchronize()
+    if repeat:
+        return out.cpu().numpy(), int(cyc.item())
     return out.cpu().numpy()
 
 
@@ -91,3 +95,4 @@ def test_mn_major_both_operands(cuda):
             lanes = [int(np.argmin(np.abs(D - want[m]).sum(1))) for m in range(0, M, 8)]
             raise AssertionError("M=64 tile mismatch, max err %g; lanes of rows 0,8,..: %s"
                                  % (np.abs(got - want).max(), lanes))
+

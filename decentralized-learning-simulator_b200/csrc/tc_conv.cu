@@ -107,8 +107,10 @@ struct ConvTcCfg {
     static constexpr int TMEM_COLS = (2 * COUT <= 64) ? 64 : 128;
 };
 
+constexpr int CT_THREADS = 256;       // warps 0-3 also run the TMEM epilogue; all warps stage operands
+
 template <int CIN, int COUT, int H, int SB, bool BIAS>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
                const __nv_bfloat16 *__restrict__ wprep, int wprep_off, int bias_off)
 {
@@ -139,16 +141,16 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(wprep + (int64_t)m * TC_PREP_ELEMS + wprep_off);
         uint4 *dst = reinterpret_cast<uint4 *>(sB);
-        for (int i = t; i < C::B_BYTES / 16; i += 128) dst[i] = __ldg(src + i);
+        for (int i = t; i < C::B_BYTES / 16; i += CT_THREADS) dst[i] = __ldg(src + i);
         uint4 *za = reinterpret_cast<uint4 *>(sA);
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-        for (int i = t; i < C::A_BYTES / 16; i += 128) za[i] = z;
+        for (int i = t; i < C::A_BYTES / 16; i += CT_THREADS) za[i] = z;
         if (t < COUT) sbias[t] = BIAS ? row[bias_off + t] : 0.f;
     }
     if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
     __syncthreads();
-    stage_items<4>(t, n_s * H * H * C::NCH, 128, [&](int i, const float *&src, uint8_t *&dst) {
+    stage_items<8>(t, n_s * H * H * C::NCH, CT_THREADS, [&](int i, const float *&src, uint8_t *&dst) {
         const int ch = i % C::NCH, q = i / C::NCH, s = q / (H * H), pix = q - s * (H * H);
         const int y = pix / H, x = pix - y * H;
         const int slot = g * p.gs + s0 + s;
@@ -189,27 +191,29 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     for (int tile = 0; tile < n_tiles; ++tile) {
         if (t == 0 && tile + 1 < n_tiles) issue(tile + 1);
         __syncwarp();
-        tc::mbar_wait(&bars[tile & 1], (uint32_t)((tile >> 1) & 1));
-        tc::fence_after_sync();
-        const int o = tile * 128 + t;                       // origin handled by this thread (TMEM lane t)
-        const int s = o / C::NPS, loc = o - s * C::NPS;
-        const int oy = loc / C::PP, ox = loc - oy * C::PP;
-        const bool valid = (s < n_s) && (oy < H) && (ox < H) && (p.img_idx[g * p.gs + s0 + (s < n_s ? s : 0)] >= 0);
-        float *dst = out + (int64_t)(g * p.gs + s0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
+        if (warp < 4) {
+            tc::mbar_wait(&bars[tile & 1], (uint32_t)((tile >> 1) & 1));
+            tc::fence_after_sync();
+            const int o = tile * 128 + t;                   // origin handled by this thread (TMEM lane t)
+            const int s = o / C::NPS, loc = o - s * C::NPS;
+            const int oy = loc / C::PP, ox = loc - oy * C::PP;
+            const bool valid = (s < n_s) && (oy < H) && (ox < H) && (p.img_idx[g * p.gs + s0 + (s < n_s ? s : 0)] >= 0);
+            float *dst = out + (int64_t)(g * p.gs + s0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
 #pragma unroll
-        for (int c0 = 0; c0 < COUT; c0 += 32) {
-            uint32_t r[32];
-            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((tile & 1) * COUT + c0), r);
-            tc::tmem_ld_wait();
-            if (valid) {
+            for (int c0 = 0; c0 < COUT; c0 += 32) {
+                uint32_t r[32];
+                tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((tile & 1) * COUT + c0), r);
+                tc::tmem_ld_wait();
+                if (valid) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    float4 v;
-                    v.x = __uint_as_float(r[j]) + sbias[c0 + j];
-                    v.y = __uint_as_float(r[j + 1]) + sbias[c0 + j + 1];
-                    v.z = __uint_as_float(r[j + 2]) + sbias[c0 + j + 2];
-                    v.w = __uint_as_float(r[j + 3]) + sbias[c0 + j + 3];
-                    *reinterpret_cast<float4 *>(dst + c0 + j) = v;
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 v;
+                        v.x = __uint_as_float(r[j]) + sbias[c0 + j];
+                        v.y = __uint_as_float(r[j + 1]) + sbias[c0 + j + 1];
+                        v.z = __uint_as_float(r[j + 2]) + sbias[c0 + j + 2];
+                        v.w = __uint_as_float(r[j + 3]) + sbias[c0 + j + 3];
+                        *reinterpret_cast<float4 *>(dst + c0 + j) = v;
+                    }
                 }
             }
         }
@@ -237,7 +241,7 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
         attr = true;
     }
     const int chunks = (p.gs + SB - 1) / SB;
-    conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * chunks, 128, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
+    conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * chunks, CT_THREADS, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
                                                                                     bias_off);
     DLS_LAUNCH_CHECK();
     return 0;

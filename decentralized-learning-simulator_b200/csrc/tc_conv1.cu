@@ -60,7 +60,9 @@ __device__ __forceinline__ void build_expanded(const uint8_t *simg, const __nv_b
 
 constexpr int C1F_SMEM = 2 * E_PLANE + C1_W_BYTES + 32 * 256 * 4 + 32 * 225 * 4 + 3072 + 512 + 32 * 4 + 32 * 4 + 64;
 
-__global__ void __launch_bounds__(128, 2)
+constexpr int C1F_THREADS = 256;      // warps 0-3 drain TMEM; all warps expand the image, pool and normalise
+
+__global__ void __launch_bounds__(C1F_THREADS, 2)
 conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -84,17 +86,17 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
-        for (int i = t; i < IMG_BYTES / 16; i += 128) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
+        for (int i = t; i < IMG_BYTES / 16; i += C1F_THREADS) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
         const uint4 *wsrc = reinterpret_cast<const uint4 *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
                                                              (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
-        for (int i = t; i < C1_W_BYTES / 16; i += 128) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
-        for (int i = t; i < 256; i += 128) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
+        for (int i = t; i < C1_W_BYTES / 16; i += C1F_THREADS) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
+        for (int i = t; i < 256; i += C1F_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
         if (t < 32) sbias[t] = row[OFF_B1 + t];
     }
     if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 64);
     __syncthreads();
-    build_expanded(simg, lut, sE, t, 128);
+    build_expanded(simg, lut, sE, t, C1F_THREADS);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -115,9 +117,9 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 
     uint8_t *idx_out = ws.idx1 ? ws.idx1 + (int64_t)slot * A1_SZ : nullptr;
     for (int k = 0; k < 8; ++k) {
-        tc::mbar_wait(&bars[k & 1], (uint32_t)((k >> 1) & 1));
-        tc::fence_after_sync();
-        {
+        if (warp < 4) {
+            tc::mbar_wait(&bars[k & 1], (uint32_t)((k >> 1) & 1));
+            tc::fence_after_sync();
             uint32_t r[32];
             tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((k & 1) * 32), r);
             tc::tmem_ld_wait();
@@ -132,7 +134,7 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
         if (t == 0 && k + 2 < 8) issue(k + 2);
         // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins)
         const int py_lo = (k == 0) ? 0 : 2 * k - 1, n_py = (k == 0) ? 1 : 2;
-        for (int o = t; o < n_py * 15 * 32; o += 128) {
+        for (int o = t; o < n_py * 15 * 32; o += C1F_THREADS) {
             const int co = o / (n_py * 15), q = o - co * (n_py * 15), py = py_lo + q / 15, px = q % 15;
             float best = -INFINITY;
             int bi = 0;
@@ -153,12 +155,12 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 
     // GroupNorm(2, 32) over 16 channels x 225 pixels per group, then ReLU (ps is channel-major)
     float s0 = 0.f, s1 = 0.f;
-    for (int e = t; e < A1_SZ; e += 128) { const float v = ps[e]; if (e < 3600) s0 += v; else s1 += v; }
+    for (int e = t; e < A1_SZ; e += C1F_THREADS) { const float v = ps[e]; if (e < 3600) s0 += v; else s1 += v; }
     const float sum0 = block_sum(s0, red), sum1 = block_sum(s1, red);
     const float inv_n = 1.f / 3600.f;
     const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
     float q0 = 0.f, q1 = 0.f;
-    for (int e = t; e < A1_SZ; e += 128) {
+    for (int e = t; e < A1_SZ; e += C1F_THREADS) {
         const float d = ps[e] - (e < 3600 ? mean0 : mean1);
         if (e < 3600) q0 = fmaf(d, d, q0); else q1 = fmaf(d, d, q1);
     }
@@ -169,7 +171,7 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
     const int co = t & 31;
     const float gam = row[OFF_G1W + co], bet = row[OFF_G1B + co];
     const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
-    for (int i = t; i < A1_SZ; i += 128) {                  // i = pp*32 + co (128 % 32 == 0: co fixed per thread)
+    for (int i = t; i < A1_SZ; i += C1F_THREADS) {          // i = pp*32 + co (256 % 32 == 0: co fixed per thread)
         const float x = ps[co * 225 + (i >> 5)];
         const float v = (x - mean) * rstd * gam + bet;
         a1[i] = v > 0.f ? v : 0.f;
@@ -251,17 +253,38 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
                 const uint8_t *ix = ws.idx1 + (int64_t)slot * A1_SZ;
                 // windows of one colour (py%2, px%2) never touch the same conv position, so the
                 // read-modify-write below is race free within a pass and the sum order is fixed
+                // all global loads of the four passes are issued up front (registers), so that the passes
+                // themselves only touch shared memory between the producer barriers
+                constexpr int MAXIT = 10;                       // ceil(8*8*32 / 224)
+                float dv[4][MAXIT];
+                uint32_t cell[4][MAXIT];                        // byte offset of the bf16 cell, 0xffffffff = none
+#pragma unroll
                 for (int colour = 0; colour < 4; ++colour) {
                     const int cy = colour >> 1, cx = colour & 1;
                     const int ny = (15 - cy + 1) / 2, nx = (15 - cx + 1) / 2;
-                    for (int i = pt; i < ny * nx * 32; i += C1W_PRODUCERS) {
-                        const int co = i & 31, w = i >> 5, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
-                        const int pp = py * 15 + px;
-                        const float d = dp[pp * 32 + co];
-                        const int ii = ix[pp * 32 + co];
-                        const int o = (2 * py + ii / 3) * 32 + 2 * px + ii % 3;
-                        __nv_bfloat16 *cell = reinterpret_cast<__nv_bfloat16 *>(sD + (co >> 3) * DC_PLANE + o * 16) + (co & 7);
-                        *cell = __float2bfloat16_rn(__bfloat162float(*cell) + d);
+#pragma unroll
+                    for (int it = 0; it < MAXIT; ++it) {
+                        const int i = pt + it * C1W_PRODUCERS;
+                        cell[colour][it] = 0xffffffffu;
+                        dv[colour][it] = 0.f;
+                        if (i < ny * nx * 32) {
+                            const int co = i & 31, w = i >> 5, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
+                            const int pp = py * 15 + px;
+                            dv[colour][it] = __ldg(dp + pp * 32 + co);
+                            const int ii = __ldg(ix + pp * 32 + co);
+                            const int o = (2 * py + ii / 3) * 32 + 2 * px + ii % 3;
+                            cell[colour][it] = (uint32_t)((co >> 3) * DC_PLANE + o * 16 + (co & 7) * 2);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int colour = 0; colour < 4; ++colour) {
+#pragma unroll
+                    for (int it = 0; it < MAXIT; ++it) {
+                        if (cell[colour][it] != 0xffffffffu) {
+                            __nv_bfloat16 *c = reinterpret_cast<__nv_bfloat16 *>(sD + cell[colour][it]);
+                            *c = __float2bfloat16_rn(__bfloat162float(*c) + dv[colour][it]);
+                        }
                     }
                     producer_sync();
                 }
@@ -370,7 +393,7 @@ int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    conv1_tc_kernel<<<p.n_groups * p.gs, 128, C1F_SMEM, st>>>(p, ws, save ? 1 : 0);
+    conv1_tc_kernel<<<p.n_groups * p.gs, C1F_THREADS, C1F_SMEM, st>>>(p, ws, save ? 1 : 0);
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -61,8 +61,10 @@ def test_dpsgd_mini_matches_reference(cuda, golden_dir, tmp_path, agg_variant):
 
 def test_dpsgd_mini_bf16_tensor_core_path(cuda, golden_dir, tmp_path):
     """Same reference graph on the precision-1 path (bf16 tcgen05 convolutions, fp32 accumulate):
-    per-round parameters within the north-star bound of 1e-3 relative; accuracy within 2 of the 256
-    test images (0.78 pp; the 0.5 pp bound is meant for the 10 000-image split) and loss within 2e-2."""
+    per-round parameters within the north-star bound of 1e-3 relative and loss within 2e-2.  After
+    three rounds the model is still at chance level (16 %), where predictions flip with the last
+    bits of the logits, so accuracy is only held to 4 of the 256 test images here; the 0.5 pp
+    criterion is asserted on a trained model in test_accuracy_trajectory_fp32_bf16_oracle."""
     g, meta, dag, st, ds = mini(golden_dir, tmp_path, cuda)
     st.precision = 1
     ex = WaveExecutor(st, ds)
@@ -73,9 +75,45 @@ def test_dpsgd_mini_bf16_tensor_core_path(cuda, golden_dir, tmp_path):
         want = str(g["acc_csv"][peer]).strip().split("\n")[1].split(",")
         got = open(os.path.join(str(tmp_path), "accuracies_%d.csv" % peer)).read().strip().split("\n")[1].split(",")
         assert got[:7] == want[:7]
-        assert abs(float(got[7]) - float(want[7])) <= 2 * 100.0 / meta["n_test"] + 1e-9
+        assert abs(float(got[7]) - float(want[7])) <= 4 * 100.0 / meta["n_test"] + 1e-9
         assert abs(float(got[8]) - float(want[8])) < 2e-2
     assert rel(final[0], g["final_node0"]) < 1e-3
+
+
+def test_accuracy_trajectory_fp32_bf16_oracle(cuda, tmp_path):
+    """Accuracy trajectory on a run long enough to learn the synthetic task (8 nodes, ring, 24 rounds
+    x 4 local steps, test every 8 rounds on 512 images): the fp32 path, the bf16 tensor-core path
+    and the CPU oracle must agree within 0.5 percentage points of mean accuracy once trained (rounds
+    16 and 24: the north-star "final test accuracy within 0.5 pp"), and within 2 pp at round 8, which
+    sits on the steepest part of the learning curve (10 % -> 100 % within a few rounds)."""
+    from oracle import oracle as O
+    n, rounds, steps, n_i, n_test, ti = 8, 24, 4, 128, 512, 8
+    dag = synthetic.dpsgd_dag(n, rounds, synthetic.ring_topology(n), test_interval=ti)
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(n_test, 32, 3, 10)
+    torch.set_num_threads(4)
+    _, acc_o = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=42, batch=32, local_steps=steps, lr=0.002, mu=0.9,
+                           wd=0.0, n_i=n_i, minibatch_permutation=synthetic.minibatch_permutation)
+    traj = {"oracle": {}}
+    for peer, rnd, t_us, a, l in acc_o:
+        traj["oracle"].setdefault(rnd, []).append(a)
+    for name, prec in (("fp32", 0), ("bf16", 1)):
+        d = tmp_path / name
+        st = SessionSettings(participants=n, seed=42, data_dir=str(d), precision=prec,
+                             learning=LearningSettings(0.002, 0.9, 0.0, 32, steps))
+        ds = DeviceDataset.synthetic(L, n, n_i, n_test, cuda, seed=42)
+        BatchedSolver(WaveExecutor(st, ds), dag).plan().run()
+        traj[name] = {}
+        for peer in range(n):
+            for line in open(os.path.join(str(d), "accuracies_%d.csv" % peer)).read().strip().split("\n")[1:]:
+                f = line.split(",")
+                traj[name].setdefault(int(f[5]), []).append(float(f[7]))
+    means = {k: {r: float(np.mean(v)) for r, v in t.items()} for k, t in traj.items()}
+    assert sorted(means["oracle"]) == [8, 16, 24]
+    for r, tol in ((8, 2.0), (16, 0.5), (24, 0.5)):
+        assert abs(means["fp32"][r] - means["oracle"][r]) <= tol, means
+        assert abs(means["bf16"][r] - means["oracle"][r]) <= tol, means
+    assert means["oracle"][24] > 80.0, means
 
 
 def test_functions_api_single_tasks(cuda, golden_dir, tmp_path):

@@ -66,7 +66,7 @@ __device__ __forceinline__ uint4 pack_bf16x8(const float4 a, const float4 b) {
 // latency bound otherwise).  `loc(i, src, dst)` maps item i to its fp32 source (nullptr = zeros) and
 // its 16-byte shared-memory destination.
 template <int U, typename Loc>
-__device__ __forceinline__ void stage_items(int first, int n_items, int stride, Loc loc) {
+__device__ __forceinline__ void stage_items(int first, int n_items, int stride, Loc loc, int dup_off = 0) {
     for (int base = first; base < n_items; base += U * stride) {
         float4 a[U], b[U];
         uint8_t *dst[U];
@@ -87,7 +87,11 @@ __device__ __forceinline__ void stage_items(int first, int n_items, int stride, 
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
-            if (dst[u]) *reinterpret_cast<uint4 *>(dst[u]) = pack_bf16x8(a[u], b[u]);
+            if (dst[u]) {
+                const uint4 v = pack_bf16x8(a[u], b[u]);
+                *reinterpret_cast<uint4 *>(dst[u]) = v;
+                if (dup_off) *reinterpret_cast<uint4 *>(dst[u] + dup_off) = v;     // second (shifted) copy
+            }
     }
 }
 
@@ -309,18 +313,25 @@ struct WgradTcCfg {
 constexpr int WG_THREADS = 256;
 constexpr int WG_PRODUCERS = WG_THREADS - 32;
 
-template <int COUT, int H, int SB>
+// PAIR (COUT == 32): instead of four zero planes, rows 32..63 of the M = 64 operand hold a second
+// copy of dY shifted by one pixel.  sum_p dY[p-1] * in[p + s] = sum_q dY[q] * in[q + s + 1], so the
+// upper half of the accumulator is the weight gradient of the NEXT tap in x: one MMA yields taps
+// (ky,kx) and (ky,kx+1), 15 MMAs per K step cover all 25 taps (480 TMEM columns) and one CTA serves
+// a whole node.
+template <int COUT, int H, int SB, bool PAIR>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws, int w_off)
 {
     using C = WgradTcCfg<COUT, H, SB>;
+    static_assert(!PAIR || (COUT == 32 && C::NPD > SB * C::NPS), "pair trick needs a spare plane entry");
+    constexpr int NMMA = PAIR ? 15 : C::TAPS0;           // accumulator tiles (32 columns each) per CTA
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + 2 * C::BUF);   // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int g = blockIdx.x >> 1, half = blockIdx.x & 1;
+    const int g = PAIR ? blockIdx.x : (blockIdx.x >> 1), half = PAIR ? 0 : (blockIdx.x & 1);
     if (p.gcount[g] <= 0) return;
-    const int tap0 = half ? C::TAPS0 : 0, ntap = half ? 25 - C::TAPS0 : C::TAPS0;
+    const int tap0 = half ? C::TAPS0 : 0, ntap = PAIR ? 15 : (half ? 25 - C::TAPS0 : C::TAPS0);
     const int gs = p.gs, n_chunks = (gs + SB - 1) / SB;
 
     {   // zero both buffers once: padding borders, K tail and (conv2) the four unused dY planes stay zero
@@ -354,7 +365,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const bool ok = sl < gs && oy < H && ox < H && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
                 src = ok ? dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8 : nullptr;
                 dst = sD + ch * C::PLANE_D + pix * 16;
-            });
+            }, PAIR ? 4 * C::PLANE_D + 16 : 0);
             stage_items<4>(pt, SB * H * H * 4, WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
                 const int y = pix / H, x = pix - y * H;
@@ -370,11 +381,15 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         // ------------------------------ MMA issuer ------------------------------
         const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
         uint32_t acc = 0;
-        uint32_t tshift[C::TAPS0];                   // tap shift in 16-byte units (registers: loops are unrolled)
+        uint32_t tshift[NMMA];                       // tap shift in 16-byte units (registers: loops are unrolled)
 #pragma unroll
-        for (int ti = 0; ti < C::TAPS0; ++ti) {
-            const int tap = tap0 + (ti < ntap ? ti : 0);
-            tshift[ti] = (uint32_t)((tap / 5) * C::PP + (tap % 5));
+        for (int ti = 0; ti < NMMA; ++ti) {
+            if (PAIR) {
+                tshift[ti] = (uint32_t)((ti / 3) * C::PP + 2 * (ti % 3));       // (ky, kx = 0,2,4)
+            } else {
+                const int tap = tap0 + (ti < ntap ? ti : 0);
+                tshift[ti] = (uint32_t)((tap / 5) * C::PP + (tap % 5));
+            }
         }
         for (int c = 0; c < n_chunks; ++c) {
             const int b = c & 1;
@@ -388,7 +403,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const uint64_t ad = ad0 + (uint64_t)(j * 16);
                 const uint64_t bdj = bd0 + (uint64_t)(j * 16);
 #pragma unroll
-                for (int ti = 0; ti < C::TAPS0; ++ti)
+                for (int ti = 0; ti < NMMA; ++ti)
                     if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
                 acc = 1;
             }
@@ -403,13 +418,21 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         tc::fence_after_sync();
         float *G = ws.G + (int64_t)g * ws.ldg + w_off;
         // an M = 64 accumulator keeps rows 16q .. 16q+15 in lanes 0..15 of TMEM quadrant q
-        const int co = warp * 16 + lane;
+        const int mrow = warp * 16 + lane;
         for (int ti = 0; ti < ntap; ++ti) {
             uint32_t r[32];
             tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ti * 32), r);
             tc::tmem_ld_wait();
-            if (lane < 16 && co < COUT) {
-                float *dst = G + (co * 32) * 25 + (tap0 + ti);
+            int co = mrow, tap = tap0 + ti;
+            bool ok = lane < 16 && mrow < COUT;
+            if (PAIR) {
+                const int kx = 2 * (ti % 3) + (mrow >> 5);          // rows 32..63: the tap one pixel to the right
+                co = mrow & 31;
+                tap = (ti / 3) * 5 + kx;
+                ok = lane < 16 && kx < 5;
+            }
+            if (ok) {
+                float *dst = G + (co * 32) * 25 + tap;
 #pragma unroll
                 for (int ci = 0; ci < 32; ++ci) dst[ci * 25] = __uint_as_float(r[ci]);
             }
@@ -446,19 +469,20 @@ conv_bias_grad_kernel(const float *__restrict__ dY, Pass p, Workspace ws, int b_
     }
 }
 
-template <int COUT, int H, int SB>
+template <int COUT, int H, int SB, bool PAIR>
 static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Workspace &ws, int w_off, int b_off,
                            cudaStream_t st)
 {
     using C = WgradTcCfg<COUT, H, SB>;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB>,
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB, PAIR>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    conv_wgrad_tc_kernel<COUT, H, SB><<<p.n_groups * 2, WG_THREADS, C::SMEM, st>>>(in, dY, p, ws, w_off);
+    conv_wgrad_tc_kernel<COUT, H, SB, PAIR><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(in, dY, p, ws,
+                                                                                                      w_off);
     DLS_LAUNCH_CHECK();
     conv_bias_grad_kernel<COUT, H><<<p.n_groups, 256, 0, st>>>(dY, p, ws, b_off);
     DLS_LAUNCH_CHECK();
@@ -467,11 +491,11 @@ static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Work
 
 int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_wgrad_tc<32, 15, 1>(ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2, st);
+    return launch_wgrad_tc<32, 15, 1, true>(ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2, st);
 }
 int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_wgrad_tc<64, 7, 4>(ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3, st);
+    return launch_wgrad_tc<64, 7, 4, false>(ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3, st);
 }
 
 }  // namespace gnl

@@ -430,7 +430,7 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     const float mean = st[grp * 2], rstd = st[grp * 2 + 1];
     const float gam = row[gw_off + ch];
 
-    float s1 = 0.f, s2 = 0.f;
+    float s1 = 0.f, s2 = 0.f, dgam = 0.f, dbet = 0.f;     // 256 % C == 0: a thread only sees channel `ch`
     for (int e = t; e < SZ; e += 256) {
         float d;
         if (POOL) {
@@ -453,6 +453,8 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
         const float dxh = d * gam;
         s1 += dxh;
         s2 = fmaf(dxh, xhat, s2);
+        dgam = fmaf(d, xhat, dgam);
+        dbet += d;
     }
     const float a0 = block_sum(grp == 0 ? s1 : 0.f, red);
     const float a1 = block_sum(grp == 1 ? s1 : 0.f, red);
@@ -465,19 +467,19 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
         const float xhat = (cp[e] - mean) * rstd;
         dst[e] = rstd * (dg[e] * gam - m1 - xhat * m2);
     }
-    // per-channel parameter-gradient partials of this sample (dg complete after the block_sum syncs)
+    // per-channel parameter-gradient partials of this sample: combine the 256/C threads of a channel
+    // in a fixed order (dg is dead now: reuse it as scratch after a barrier)
+    __syncthreads();
+    dg[t] = dgam;
+    dg[256 + t] = dbet;
+    __syncthreads();
     if (t < C) {
-        const int gr = t >= (C / 2);
-        const float mn = st[gr * 2], rs = st[gr * 2 + 1];
-        float dgam = 0.f, dbet = 0.f;
-        for (int pix = 0; pix < H * H; ++pix) {
-            const float d = dg[pix * C + t];
-            dgam = fmaf(d, (cp[pix * C + t] - mn) * rs, dgam);
-            dbet += d;
-        }
+        float sg = 0.f, sb = 0.f;
+#pragma unroll
+        for (int j = 0; j < 256 / C; ++j) { sg += dg[t + j * C]; sb += dg[256 + t + j * C]; }
         float *o = gnp + (int64_t)slot * GNP_SZ + gnp_off;
-        o[t] = dgam;
-        o[C + t] = dbet;
+        o[t] = sg;
+        o[C + t] = sb;
     }
 }
 
@@ -593,9 +595,9 @@ int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st)
     dim3 grid(8, p.n_models);
     // in train passes model index == group index, so gcount doubles as the "model active" mask
     const int32_t *active = p.gmodel ? nullptr : p.gcount;
+    if (ws.precision == 1) return prep_weights_tc(p, ws, backward, st);   // bf16 UMMA layouts only
     prep_weights_kernel<<<grid, 256, 0, st>>>(p, ws.prep, backward ? 1 : 0, active);
     DLS_LAUNCH_CHECK();
-    if (ws.precision == 1) return prep_weights_tc(p, ws, backward, st);
     return 0;
 }
 

@@ -358,7 +358,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));   // MMAs of chunk c-2 done
             uint8_t *sD = smem + b * C::BUF;
             uint8_t *sI = sD + 8 * C::PLANE_D;
-            stage_items<4>(pt, SB * C::NPS * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
+            stage_items<8>(pt, SB * C::NPS * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
                 const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
                 const int sl = c * SB + s;

@@ -107,126 +107,157 @@ struct ConvTcCfg {
     static constexpr int KCH = 25 * NCH;                   // 8-element K chunks
     static constexpr int B_BYTES = KCH * COUT * 16;
     static constexpr int A_BYTES = NCH * PLANE;
-    static constexpr int SMEM = B_BYTES + A_BYTES + COUT * 4 + 64;
+    static constexpr int SMEM = B_BYTES + 2 * A_BYTES + COUT * 4 + 128;
     static constexpr int TMEM_COLS = (2 * COUT <= 64) ? 64 : 128;
 };
 
-constexpr int CT_THREADS = 256;       // warps 0-3 also run the TMEM epilogue; all warps stage operands
+// Warp-specialised, persistent over the samples of a node (or half a node):
+//   warps 0-3  epilogue: TMEM -> registers -> (+bias) -> global, one TMEM lane quadrant each
+//   warp  4    MMA issuer (one elected lane)
+//   warps 5-7  producers: fp32 NHWC activations -> bf16 planes of chunk c+1 while chunk c is consumed
+// Shared memory: the node's weights (loaded once per CTA) + two activation buffers of SB samples.
+// mbarriers: full[b]/empty[b] per activation buffer, tfull[t]/tempty[t] per TMEM accumulator buffer.
+constexpr int CT_THREADS = 256;
+constexpr int CT_PRODUCERS = 96;
 
 template <int CIN, int COUT, int H, int SB, bool BIAS>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
-               const __nv_bfloat16 *__restrict__ wprep, int wprep_off, int bias_off)
+               const __nv_bfloat16 *__restrict__ wprep, int wprep_off, int bias_off, int spc)
 {
     using C = ConvTcCfg<CIN, COUT, H, SB>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *sB = smem;
-    uint8_t *sA = smem + C::B_BYTES;
-    float *sbias = reinterpret_cast<float *>(sA + C::A_BYTES);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sbias + COUT);       // 2 mbarriers
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+    uint8_t *sA0 = smem + C::B_BYTES;
+    float *sbias = reinterpret_cast<float *>(sA0 + 2 * C::A_BYTES);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sbias + COUT);       // full[2] empty[2] tfull[2] tempty[2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
 
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int chunks = (p.gs + SB - 1) / SB;
-    const int g = blockIdx.x / chunks, chunk = blockIdx.x - g * chunks;
-    const int s0 = chunk * SB;
-    const int cnt = p.gcount[g];
-    if (cnt <= 0) return;
-    int n_s = p.gs - s0;
-    if (n_s > SB) n_s = SB;
-    // active samples of this chunk (empty slots carry img_idx < 0; they are always at the tail)
-    int n_act = 0;
-    for (int s = 0; s < n_s; ++s) n_act += (p.img_idx[g * p.gs + s0 + s] >= 0) ? 1 : 0;
-    if (n_act == 0) return;
+    const int parts = (p.gs + spc - 1) / spc;
+    const int g = blockIdx.x / parts, part = blockIdx.x - g * parts;
+    if (p.gcount[g] <= 0) return;
+    const int s_begin = part * spc;
+    int s_end = s_begin + spc;
+    if (s_end > p.gs) s_end = p.gs;
+    // empty slots (img_idx < 0) sit at the tail of a group: stop at the last active sample
+    while (s_end > s_begin && p.img_idx[g * p.gs + s_end - 1] < 0) --s_end;
+    if (s_end <= s_begin) return;
+    const int n_chunks = (s_end - s_begin + SB - 1) / SB;
     int m;
     const float *row = model_row(p, g, m);
 
-    // ---- stage weights (already in UMMA layout) and activations (fp32 NHWC -> bf16 planes) ----
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(wprep + (int64_t)m * TC_PREP_ELEMS + wprep_off);
         uint4 *dst = reinterpret_cast<uint4 *>(sB);
         for (int i = t; i < C::B_BYTES / 16; i += CT_THREADS) dst[i] = __ldg(src + i);
-        uint4 *za = reinterpret_cast<uint4 *>(sA);
+        uint4 *za = reinterpret_cast<uint4 *>(sA0);
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-        for (int i = t; i < C::A_BYTES / 16; i += CT_THREADS) za[i] = z;
+        for (int i = t; i < 2 * C::A_BYTES / 16; i += CT_THREADS) za[i] = z;
         if (t < COUT) sbias[t] = BIAS ? row[bias_off + t] : 0.f;
     }
-    if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
+    if (t == 0) {
+        tc::mbar_init(&bars[0], CT_PRODUCERS); tc::mbar_init(&bars[1], CT_PRODUCERS);
+        tc::mbar_init(&bars[2], 1); tc::mbar_init(&bars[3], 1);
+        tc::mbar_init(&bars[4], 1); tc::mbar_init(&bars[5], 1);
+        tc::mbar_init(&bars[6], 128); tc::mbar_init(&bars[7], 128);
+        tc::mbar_fence_init();
+    }
     if (warp == 0) tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
-    __syncthreads();
-    stage_items<8>(t, n_s * H * H * C::NCH, CT_THREADS, [&](int i, const float *&src, uint8_t *&dst) {
-        const int ch = i % C::NCH, q = i / C::NCH, s = q / (H * H), pix = q - s * (H * H);
-        const int y = pix / H, x = pix - y * H;
-        const int slot = g * p.gs + s0 + s;
-        src = (p.img_idx[slot] >= 0) ? in + (int64_t)slot * (H * H * CIN) + pix * CIN + ch * 8 : nullptr;
-        dst = sA + ch * C::PLANE + (s * C::NPS + (y + 2) * C::PP + (x + 2)) * 16;
-    });
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-
     const uint32_t tmem = *tmem_slot;
-    const uint32_t a_base = tc::smem_u32(sA), b_base = tc::smem_u32(sB);
-    const uint32_t idesc = tc::instr_desc_bf16(128, COUT, 0, 0);
-    const int n_origins = (n_s - 1) * C::NPS + C::LAST;
-    const int n_tiles = (n_origins + 127) / 128;
 
-    // Descriptors differ between MMAs only in their 14-bit start-address field (address >> 4); all
-    // per-tap / per-K-step offsets are compile-time constants of the fully unrolled loops, so the
-    // single issuing thread spends two integer adds per MMA.
-    const uint64_t bd0 = tc::smem_desc(b_base, COUT * 16, 128);
-    auto issue = [&](int tile) {
-        const uint32_t d = tmem + (uint32_t)((tile & 1) * COUT);
-        const uint64_t ad_tile = tc::smem_desc(a_base + (uint32_t)tile * 2048u, C::PLANE, 128);
+    auto chunk_samples = [&](int c) { const int r = (s_end - s_begin) - c * SB; return r < SB ? r : SB; };
+    auto chunk_tiles = [&](int c) { return ((chunk_samples(c) - 1) * C::NPS + C::LAST + 127) / 128; };
+
+    if (warp >= 5) {
+        // ------------------------------ producers ------------------------------
+        const int pt = t - 160;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b = c & 1;
+            if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));
+            uint8_t *sA = sA0 + b * C::A_BYTES;
+            const int ns = chunk_samples(c), slot0 = g * p.gs + s_begin + c * SB;
+            stage_items<8>(pt, ns * H * H * C::NCH, CT_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
+                const int ch = i % C::NCH, q = i / C::NCH, s = q / (H * H), pix = q - s * (H * H);
+                const int y = pix / H, x = pix - y * H;
+                src = in + (int64_t)(slot0 + s) * (H * H * CIN) + pix * CIN + ch * 8;
+                dst = sA + ch * C::PLANE + (s * C::NPS + (y + 2) * C::PP + (x + 2)) * 16;
+            });
+            tc::fence_async_smem();
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
+        }
+    } else if (warp == 4) {
+        // ------------------------------ MMA issuer ------------------------------
+        if (lane == 0) {
+            const uint32_t idesc = tc::instr_desc_bf16(128, COUT, 0, 0);
+            const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sB), COUT * 16, 128);
+            int gt = 0;
+            for (int c = 0; c < n_chunks; ++c) {
+                const int b = c & 1;
+                tc::mbar_wait(&bars[b], (uint32_t)((c >> 1) & 1));
+                tc::fence_after_sync();
+                const uint32_t a_base = tc::smem_u32(sA0 + b * C::A_BYTES);
+                const int nt = chunk_tiles(c);
+                for (int tile = 0; tile < nt; ++tile, ++gt) {
+                    const int tb = gt & 1;
+                    if (gt >= 2) { tc::mbar_wait(&bars[6 + tb], (uint32_t)(((gt >> 1) - 1) & 1)); tc::fence_after_sync(); }
+                    const uint32_t d = tmem + (uint32_t)(tb * COUT);
+                    const uint64_t ad_tile = tc::smem_desc(a_base + (uint32_t)tile * 2048u, C::PLANE, 128);
 #pragma unroll
-        for (int tap = 0; tap < 25; ++tap) {
+                    for (int tap = 0; tap < 25; ++tap) {
 #pragma unroll
-            for (int h = 0; h < CIN / 16; ++h) {
-                const uint64_t ad = ad_tile + (uint64_t)((((tap / 5) * C::PP + (tap % 5)) * 16 + 2 * h * C::PLANE) >> 4);
-                const uint64_t bd = bd0 + (uint64_t)(((tap * C::NCH + 2 * h) * (COUT * 16)) >> 4);
-                tc::mma_f16(d, ad, bd, idesc, (tap | h) != 0 ? 1u : 0u);
+                        for (int h = 0; h < CIN / 16; ++h) {
+                            const uint64_t ad = ad_tile + (uint64_t)((((tap / 5) * C::PP + (tap % 5)) * 16 + 2 * h * C::PLANE) >> 4);
+                            const uint64_t bd = bd0 + (uint64_t)(((tap * C::NCH + 2 * h) * (COUT * 16)) >> 4);
+                            tc::mma_f16(d, ad, bd, idesc, (tap | h) != 0 ? 1u : 0u);
+                        }
+                    }
+                    tc::mma_commit(&bars[4 + tb]);
+                }
+                tc::mma_commit(&bars[2 + b]);              // activation buffer b is free once these MMAs finish
             }
         }
-        tc::mma_commit(&bars[tile & 1]);
-    };
-
-    if (t == 0) issue(0);
-    for (int tile = 0; tile < n_tiles; ++tile) {
-        if (t == 0 && tile + 1 < n_tiles) issue(tile + 1);
-        __syncwarp();
-        if (warp < 4) {
-            tc::mbar_wait(&bars[tile & 1], (uint32_t)((tile >> 1) & 1));
-            tc::fence_after_sync();
-            const int o = tile * 128 + t;                   // origin handled by this thread (TMEM lane t)
-            const int s = o / C::NPS, loc = o - s * C::NPS;
-            const int oy = loc / C::PP, ox = loc - oy * C::PP;
-            const bool valid = (s < n_s) && (oy < H) && (ox < H) && (p.img_idx[g * p.gs + s0 + (s < n_s ? s : 0)] >= 0);
-            float *dst = out + (int64_t)(g * p.gs + s0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
+    } else {
+        // ------------------------------ epilogue (warps 0-3) ------------------------------
+        int gt = 0;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int ns = chunk_samples(c), nt = chunk_tiles(c), slot0 = g * p.gs + s_begin + c * SB;
+            for (int tile = 0; tile < nt; ++tile, ++gt) {
+                const int tb = gt & 1;
+                tc::mbar_wait(&bars[4 + tb], (uint32_t)((gt >> 1) & 1));
+                tc::fence_after_sync();
+                uint32_t r[COUT];
 #pragma unroll
-            for (int c0 = 0; c0 < COUT; c0 += 32) {
-                uint32_t r[32];
-                tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((tile & 1) * COUT + c0), r);
+                for (int c0 = 0; c0 < COUT; c0 += 32)
+                    tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(tb * COUT + c0),
+                                  *reinterpret_cast<uint32_t(*)[32]>(&r[c0]));
                 tc::tmem_ld_wait();
-                if (valid) {
+                tc::fence_before_sync();
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[6 + tb])) : "memory");
+                const int o = tile * 128 + t;               // origin handled by this thread (TMEM lane t)
+                const int s = o / C::NPS, loc = o - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
+                if (s < ns && oy < H && ox < H) {
+                    float *dst = out + (int64_t)(slot0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
+                    for (int j = 0; j < COUT; j += 4) {
                         float4 v;
-                        v.x = __uint_as_float(r[j]) + sbias[c0 + j];
-                        v.y = __uint_as_float(r[j + 1]) + sbias[c0 + j + 1];
-                        v.z = __uint_as_float(r[j + 2]) + sbias[c0 + j + 2];
-                        v.w = __uint_as_float(r[j + 3]) + sbias[c0 + j + 3];
-                        *reinterpret_cast<float4 *>(dst + c0 + j) = v;
+                        v.x = __uint_as_float(r[j]) + sbias[j];
+                        v.y = __uint_as_float(r[j + 1]) + sbias[j + 1];
+                        v.z = __uint_as_float(r[j + 2]) + sbias[j + 2];
+                        v.w = __uint_as_float(r[j + 3]) + sbias[j + 3];
+                        *reinterpret_cast<float4 *>(dst + j) = v;
                     }
                 }
             }
         }
-        tc::fence_before_sync();
-        __syncthreads();                                    // everyone done with this TMEM buffer
-        tc::fence_after_sync();
     }
+    tc::fence_before_sync();
+    __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem, C::TMEM_COLS);
-    (void)lane;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -244,9 +275,12 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    const int chunks = (p.gs + SB - 1) / SB;
-    conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * chunks, CT_THREADS, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
-                                                                                    bias_off);
+    // a CTA serves a whole node when there are enough nodes to fill the GPU twice, else half a node
+    int spc = p.gs;
+    if (p.n_groups < 2 * 148 && p.gs > SB) spc = ((p.gs / 2 + SB - 1) / SB) * SB;
+    const int parts = (p.gs + spc - 1) / spc;
+    conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * parts, CT_THREADS, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
+                                                                                   bias_off, spc);
     DLS_LAUNCH_CHECK();
     return 0;
 }
@@ -263,22 +297,22 @@ int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st
 
 int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 32, 15, 4, true>(ws.a1, ws.c2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 32, 15, 3, true>(ws.a1, ws.c2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                TCO_W2U, OFF_B2, st);
 }
 int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 64, 7, 8, true>(ws.a2, ws.c3, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 64, 7, 4, true>(ws.a2, ws.c3, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                               TCO_W3U, OFF_B3, st);
 }
 int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<64, 32, 7, 4, false>(ws.dc3, ws.da2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<64, 32, 7, 2, false>(ws.dc3, ws.da2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                TCO_W3UD, 0, st);
 }
 int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 32, 15, 4, false>(ws.dc2, ws.da1, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 32, 15, 3, false>(ws.dc2, ws.da1, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                 TCO_W2UD, 0, st);
 }
 

@@ -118,7 +118,7 @@ struct ConvTcCfg {
 // Shared memory: the node's weights (loaded once per CTA) + two activation buffers of SB samples.
 // mbarriers: full[b]/empty[b] per activation buffer, tfull[t]/tempty[t] per TMEM accumulator buffer.
 constexpr int CT_THREADS = 256;
-constexpr int CT_PRODUCERS = 96;
+constexpr int CT_PRODUCERS = CT_THREADS - 160;
 
 template <int CIN, int COUT, int H, int SB, bool BIAS>
 __global__ void __launch_bounds__(CT_THREADS, 1)
@@ -330,7 +330,7 @@ int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 // (13 x 32 fp32 TMEM columns); it walks over all samples of the node, double buffering the
 // staged planes: warps 1-7 stage chunk c+1 while one thread of warp 0 issues the MMAs of chunk c.
 // ==========================================================================================
-template <int COUT, int H, int SB>
+template <int COUT, int H, int SB, bool PAIR = false>
 struct WgradTcCfg {
     static constexpr int CIN = 32;
     static constexpr int PP = H + 4;
@@ -339,7 +339,9 @@ struct WgradTcCfg {
     static constexpr int TAIL = ((4 * PP + 4 + 7) / 8) * 8;
     static constexpr int NPD = KPIX, NPI = KPIX + TAIL;
     static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
-    static constexpr int BUF = 8 * PLANE_D + 4 * PLANE_I;
+    static constexpr int MROWS = PAIR ? 2 * COUT : 64;            // accumulator rows of one MMA
+    static constexpr int DPLANES = MROWS / 8;                      // 8-channel dY planes (PAIR: two shifted copies)
+    static constexpr int BUF = DPLANES * PLANE_D + 4 * PLANE_I;
     static constexpr int SMEM = 2 * BUF + 128;
     static constexpr int TAPS0 = 13;                                // taps of CTA half 0; half 1 gets 12
 };
@@ -356,8 +358,9 @@ template <int COUT, int H, int SB, bool PAIR>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws, int w_off)
 {
-    using C = WgradTcCfg<COUT, H, SB>;
-    static_assert(!PAIR || (COUT == 32 && C::NPD > SB * C::NPS), "pair trick needs a spare plane entry");
+    using C = WgradTcCfg<COUT, H, SB, PAIR>;
+    static_assert(!PAIR || (C::NPD > SB * C::NPS), "pair trick needs a spare plane entry");
+    static_assert(PAIR || COUT == 64, "without the pair trick the operand must have 64 real rows");
     constexpr int NMMA = PAIR ? 15 : C::TAPS0;           // accumulator tiles (32 columns each) per CTA
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + 2 * C::BUF);   // full[2], empty[2], done
@@ -391,7 +394,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             const int b = c & 1;
             if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));   // MMAs of chunk c-2 done
             uint8_t *sD = smem + b * C::BUF;
-            uint8_t *sI = sD + 8 * C::PLANE_D;
+            uint8_t *sI = sD + C::DPLANES * C::PLANE_D;
             stage_items<8>(pt, SB * C::NPS * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
                 const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
@@ -399,7 +402,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const bool ok = sl < gs && oy < H && ox < H && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
                 src = ok ? dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8 : nullptr;
                 dst = sD + ch * C::PLANE_D + pix * 16;
-            }, PAIR ? 4 * C::PLANE_D + 16 : 0);
+            }, PAIR ? (COUT / 8) * C::PLANE_D + 16 : 0);
             stage_items<4>(pt, SB * H * H * 4, WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
                 const int y = pix / H, x = pix - y * H;
@@ -413,7 +416,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         }
     } else if (lane == 0) {
         // ------------------------------ MMA issuer ------------------------------
-        const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
+        const uint32_t idesc = tc::instr_desc_bf16(C::MROWS, 32, 1, 1);
         uint32_t acc = 0;
         uint32_t tshift[NMMA];                       // tap shift in 16-byte units (registers: loops are unrolled)
 #pragma unroll
@@ -431,7 +434,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             tc::fence_after_sync();
             const uint32_t d_base = tc::smem_u32(smem + b * C::BUF);
             const uint64_t ad0 = tc::smem_desc(d_base, 128, C::PLANE_D);
-            const uint64_t bd0 = tc::smem_desc(d_base + 8 * C::PLANE_D, 128, C::PLANE_I);
+            const uint64_t bd0 = tc::smem_desc(d_base + C::DPLANES * C::PLANE_D, 128, C::PLANE_I);
 #pragma unroll 1
             for (int j = 0; j < C::KPIX / 16; ++j) {
                 const uint64_t ad = ad0 + (uint64_t)(j * 16);
@@ -451,19 +454,21 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         tc::mbar_wait(&bars[4], 0);
         tc::fence_after_sync();
         float *G = ws.G + (int64_t)g * ws.ldg + w_off;
-        // an M = 64 accumulator keeps rows 16q .. 16q+15 in lanes 0..15 of TMEM quadrant q
-        const int mrow = warp * 16 + lane;
+        // an M = 64 accumulator keeps rows 16q .. 16q+15 in lanes 0..15 of TMEM quadrant q; M = 128 uses
+        // all 32 lanes of a quadrant (row = TMEM lane)
+        const int mrow = (C::MROWS == 128) ? (warp * 32 + lane) : (warp * 16 + lane);
+        const bool lane_ok = (C::MROWS == 128) || lane < 16;
         for (int ti = 0; ti < ntap; ++ti) {
             uint32_t r[32];
             tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ti * 32), r);
             tc::tmem_ld_wait();
             int co = mrow, tap = tap0 + ti;
-            bool ok = lane < 16 && mrow < COUT;
+            bool ok = lane_ok && mrow < COUT;
             if (PAIR) {
-                const int kx = 2 * (ti % 3) + (mrow >> 5);          // rows 32..63: the tap one pixel to the right
-                co = mrow & 31;
+                const int kx = 2 * (ti % 3) + (mrow >= COUT ? 1 : 0);   // upper rows: the tap one pixel to the right
+                co = mrow % COUT;
                 tap = (ti / 3) * 5 + kx;
-                ok = lane < 16 && kx < 5;
+                ok = lane_ok && kx < 5;
             }
             if (ok) {
                 float *dst = G + (co * 32) * 25 + tap;
@@ -507,7 +512,7 @@ template <int COUT, int H, int SB, bool PAIR>
 static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Workspace &ws, int w_off, int b_off,
                            cudaStream_t st)
 {
-    using C = WgradTcCfg<COUT, H, SB>;
+    using C = WgradTcCfg<COUT, H, SB, PAIR>;
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB, PAIR>,
@@ -529,7 +534,7 @@ int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 }
 int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_wgrad_tc<64, 7, 4, false>(ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3, st);
+    return launch_wgrad_tc<64, 7, 2, true>(ws.a2, ws.dc3, p, ws, OFF_W3, OFF_B3, st);
 }
 
 }  // namespace gnl

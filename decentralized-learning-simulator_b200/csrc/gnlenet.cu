@@ -430,24 +430,30 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     const float mean = st[grp * 2], rstd = st[grp * 2 + 1];
     const float gam = row[gw_off + ch];
 
+    if (POOL) {
+        // route each pooled gradient to the arg-max position of its 3x3/2 window.  Windows of one colour
+        // (py%2, px%2) are disjoint, so four passes add without races and in a fixed order.
+        const uint8_t *is = idx + (int64_t)slot * OSZ;
+        for (int e = t; e < SZ; e += 256) dg[e] = 0.f;
+        __syncthreads();
+#pragma unroll
+        for (int colour = 0; colour < 4; ++colour) {
+            const int cy = colour >> 1, cx = colour & 1;
+            const int ny = (PH - cy + 1) / 2, nx = (PH - cx + 1) / 2;
+            for (int i = t; i < ny * nx * C; i += 256) {
+                const int c = i % C, w = i / C, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
+                const int o = (py * PH + px) * C + c;
+                if (as[o] > 0.f) {
+                    const int li = is[o];
+                    dg[((2 * py + li / 3) * H + 2 * px + li % 3) * C + c] += das[o];
+                }
+            }
+            __syncthreads();
+        }
+    }
     float s1 = 0.f, s2 = 0.f, dgam = 0.f, dbet = 0.f;     // 256 % C == 0: a thread only sees channel `ch`
     for (int e = t; e < SZ; e += 256) {
-        float d;
-        if (POOL) {
-            const uint8_t *is = idx + (int64_t)slot * OSZ;
-            const int pix = e / C, y = pix / H, x = pix - y * H;
-            const int py_lo = max(0, (y - 1) / 2), py_hi = min(PH - 1, y / 2);
-            const int px_lo = max(0, (x - 1) / 2), px_hi = min(PH - 1, x / 2);
-            d = 0.f;
-            for (int py = py_lo; py <= py_hi; ++py)
-                for (int px = px_lo; px <= px_hi; ++px) {
-                    const int o = (py * PH + px) * C + ch;
-                    const int li = (y - 2 * py) * 3 + (x - 2 * px);
-                    if ((int)is[o] == li && as[o] > 0.f) d += das[o];
-                }
-        } else {
-            d = as[e] > 0.f ? das[e] : 0.f;
-        }
+        const float d = POOL ? dg[e] : (as[e] > 0.f ? das[e] : 0.f);
         dg[e] = d;
         const float xhat = (cp[e] - mean) * rstd;
         const float dxh = d * gam;
@@ -463,23 +469,28 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     const float inv_n = 1.f / (float)(SZ / 2);
     const float m1 = (grp ? a1 : a0) * inv_n, m2 = (grp ? b1 : b0) * inv_n;
     float *dst = dc + (int64_t)slot * SZ;
+    float dbias = 0.f;                                     // sum of dc per channel = conv bias gradient partial
     for (int e = t; e < SZ; e += 256) {
         const float xhat = (cp[e] - mean) * rstd;
-        dst[e] = rstd * (dg[e] * gam - m1 - xhat * m2);
+        const float v = rstd * (dg[e] * gam - m1 - xhat * m2);
+        dst[e] = v;
+        dbias += v;
     }
     // per-channel parameter-gradient partials of this sample: combine the 256/C threads of a channel
     // in a fixed order (dg is dead now: reuse it as scratch after a barrier)
     __syncthreads();
     dg[t] = dgam;
     dg[256 + t] = dbet;
+    dg[512 + t] = dbias;
     __syncthreads();
     if (t < C) {
-        float sg = 0.f, sb = 0.f;
+        float sg = 0.f, sb = 0.f, sc = 0.f;
 #pragma unroll
-        for (int j = 0; j < 256 / C; ++j) { sg += dg[t + j * C]; sb += dg[256 + t + j * C]; }
+        for (int j = 0; j < 256 / C; ++j) { sg += dg[t + j * C]; sb += dg[256 + t + j * C]; sc += dg[512 + t + j * C]; }
         float *o = gnp + (int64_t)slot * GNP_SZ + gnp_off;
         o[t] = sg;
         o[C + t] = sb;
+        o[2 * C + t] = sc;
     }
 }
 
@@ -546,8 +557,8 @@ conv1_wgrad_kernel(Pass p, Workspace ws)
     if (lane == 0) G[OFF_B1 + co] = bsum;
 }
 
-// Sum the per-sample GroupNorm parameter-gradient partials of a group in slot order.
-__global__ void __launch_bounds__(256)
+// Sum the per-sample partials (GroupNorm gamma/beta and conv bias gradients) of a group in slot order.
+__global__ void __launch_bounds__(GNP_SZ)
 gn_param_reduce_kernel(Pass p, Workspace ws)
 {
     const int g = blockIdx.x, t = threadIdx.x;
@@ -557,13 +568,16 @@ gn_param_reduce_kernel(Pass p, Workspace ws)
         const int slot = g * p.gs + k;
         if (p.img_idx[slot] >= 0) s += ws.gnp[(int64_t)slot * GNP_SZ + t];
     }
-    int dst;
+    int dst;                                  // per layer: [gamma C][beta C][conv bias C]
     if (t < 32) dst = OFF_G1W + t;
     else if (t < 64) dst = OFF_G1B + (t - 32);
-    else if (t < 96) dst = OFF_G2W + (t - 64);
-    else if (t < 128) dst = OFF_G2B + (t - 96);
-    else if (t < 192) dst = OFF_G3W + (t - 128);
-    else dst = OFF_G3B + (t - 192);
+    else if (t < 96) dst = OFF_B1 + (t - 64);
+    else if (t < 128) dst = OFF_G2W + (t - 96);
+    else if (t < 160) dst = OFF_G2B + (t - 128);
+    else if (t < 192) dst = OFF_B2 + (t - 160);
+    else if (t < 256) dst = OFF_G3W + (t - 192);
+    else if (t < 320) dst = OFF_G3B + (t - 256);
+    else dst = OFF_B3 + (t - 320);
     ws.G[(int64_t)g * ws.ldg + dst] = s;
 }
 
@@ -648,7 +662,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     const int S = p.n_groups * p.gs;
     // block 3
     gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
-                                                          ws.gnp, p, OFF_G3W, 128);
+                                                          ws.gnp, p, OFF_G3W, 192);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv3_wgrad_tc(p, ws, st))) return rc;
@@ -665,7 +679,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
     }
     // block 2
     gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
-                                                           ws.gnp, p, OFF_G2W, 64);
+                                                           ws.gnp, p, OFF_G2W, 96);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv2_wgrad_tc(p, ws, st))) return rc;
@@ -690,7 +704,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st)
         conv1_wgrad_kernel<<<dim3(p.n_groups, 4), 256, 0, st>>>(p, ws);
         DLS_LAUNCH_CHECK();
     }
-    gn_param_reduce_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
+    gn_param_reduce_kernel<<<p.n_groups, GNP_SZ, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -25,7 +25,7 @@ constexpr int C2_SZ = H2 * H2 * C2;     // 7200
 constexpr int A2_SZ = PH2 * PH2 * C2;   // 1568
 constexpr int C3_SZ = H3 * H3 * C3;     // 3136
 constexpr int A3_SZ = PH3 * PH3 * C3;   // 576
-constexpr int GNP_SZ = 2 * (C1 + C2 + C3);   // per-slot partial GN parameter gradients (256)
+constexpr int GNP_SZ = 3 * (C1 + C2 + C3);   // per-slot partials: GN gamma, GN beta, conv bias gradient (384)
 
 constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
 constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200 + 2560;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)

@@ -523,8 +523,7 @@ static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Work
     conv_wgrad_tc_kernel<COUT, H, SB, PAIR><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(in, dY, p, ws,
                                                                                                       w_off);
     DLS_LAUNCH_CHECK();
-    conv_bias_grad_kernel<COUT, H><<<p.n_groups, 256, 0, st>>>(dY, p, ws, b_off);
-    DLS_LAUNCH_CHECK();
+    (void)b_off;      // the bias gradient comes from the per-sample partials of gn_block_bwd (gn_param_reduce)
     return 0;
 }
 

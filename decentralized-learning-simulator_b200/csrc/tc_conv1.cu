@@ -372,9 +372,7 @@ int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
     }
     conv1_wgrad_tc_kernel<<<p.n_groups, C1W_THREADS, C1W_SMEM, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
-    conv1_bias_grad_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
-    DLS_LAUNCH_CHECK();
-    return 0;
+    return 0;         // conv1's bias gradient: per-sample partials of gn_block_bwd, summed by gn_param_reduce
 }
 
 int prep_w1_tc(const Pass &p, Workspace &ws, cudaStream_t st)

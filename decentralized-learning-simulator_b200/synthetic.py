@@ -59,8 +59,12 @@ def minibatch_permutations(seed: int, nodes: Sequence[int], rounds: Sequence[int
         rounds = np.asarray(rounds, dtype=np.uint64).reshape(-1, 1)
         base = _mix64(np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15) + nodes * np.uint64(0xD1B54A32D192ED03)
                       + rounds * np.uint64(0x8CB92BA72F3D8DD7) + np.uint64(0x632BE59BD9B4E019))
-        keys = _mix64(base + np.arange(n_i, dtype=np.uint64).reshape(1, -1) * np.uint64(0x9E3779B97F4A7C15))
-    return np.argsort(keys, axis=1, kind="stable").astype(np.int32)
+        idx = np.arange(n_i, dtype=np.uint64).reshape(1, -1)
+        keys = _mix64(base + idx * np.uint64(0x9E3779B97F4A7C15))
+        # the sample index in the low 24 bits makes every key unique, so the order does not depend on
+        # the sort algorithm (and the default introsort / SIMD sort can be used)
+        keys = (keys & np.uint64(0xFFFFFFFFFF000000)) | idx
+    return np.argsort(keys, axis=1).astype(np.int32)
 
 
 def minibatch_permutation(seed: int, node: int, round_nr: int, n_i: int) -> np.ndarray:
@@ -159,4 +163,48 @@ def dpsgd_dag(n: int, rounds: int, in_neighbours: List[List[int]], test_interval
                     [(name, 0)])
                 model_of[peer] = (tname, 0)
         t_us += 1_000_000
+    return list(tasks.values())
+
+
+def gossip_dag(n: int, events: int, seed: int = 0) -> List[Dict]:
+    """An asynchronous, gossip-style compute graph in the reference's task format: every event one
+    node trains on its current model and pushes the result to a random peer, which averages it with
+    its own model using age-proportional `weights` (the shape `AsynchronousClient.aggregate` builds,
+    dasklearn/simulation/asynchronous_client.py:53-74).  Wavefronts mix train and aggregate tasks,
+    fan-in is 2, and a trained model has two consumers (the peer's aggregate and the node's own
+    next train), which exercises the solver's copy-versus-in-place logic."""
+    rs = np.random.RandomState(seed)
+    tasks: Dict[str, Dict] = {}
+
+    def add(name, func, data, inputs):
+        tasks[name] = {"name": name, "func": func, "data": data, "inputs": list(inputs), "outputs": []}
+        for src, idx in inputs:
+            tasks[src]["outputs"].append((name, idx))
+
+    model_of: List[Tuple[Optional[str], int]] = [(None, 0)] * n
+    age = [0] * n
+    trains = [0] * n
+    n_train = n_agg = 0
+    order = list(range(n)) + [int(rs.randint(n)) for _ in range(events)]      # everybody trains once first
+    for e, i in enumerate(order):
+        n_train += 1
+        trains[i] += 1
+        name = "train_%d" % n_train
+        prev = model_of[i]
+        add(name, "train", {"model": prev, "round": trains[i], "time": e * 1000, "peer": i},
+            [] if prev[0] is None else [prev])
+        model_of[i] = (name, 0)
+        age[i] += 1
+        if e < n:
+            continue
+        j = int(rs.randint(n - 1))
+        j = j if j < i else j + 1
+        n_agg += 1
+        aname = "agg_%d" % n_agg
+        models = [model_of[i], model_of[j]]
+        tot = float(age[i] + age[j])
+        add(aname, "aggregate", {"models": list(models), "round": max(age[i], age[j]), "peer": j,
+                                 "weights": [age[i] / tot, age[j] / tot]}, models)
+        model_of[j] = (aname, 0)
+        age[j] = max(age[i], age[j])
     return list(tasks.values())

@@ -116,6 +116,32 @@ def test_accuracy_trajectory_fp32_bf16_oracle(cuda, tmp_path):
     assert means["oracle"][24] > 80.0, means
 
 
+def test_async_gossip_graph_mixed_wavefronts(cuda, tmp_path):
+    """Asynchronous gossip-style graph: wavefronts that mix train and aggregate tasks, age-weighted
+    fan-in-2 aggregates, trained models with two consumers (copy instead of in-place training).
+    Every sink model must match the oracle's sequential solve (fp32 path)."""
+    from oracle import oracle as O
+    n, n_i = 6, 64
+    dag = synthetic.gossip_dag(n, 14, seed=3)
+    st = SessionSettings(participants=n, seed=42, data_dir=str(tmp_path), learning=LearningSettings(0.002, 0.9, 0.0, 32, 2))
+    ds = DeviceDataset.synthetic(L, n, n_i, 32, cuda, seed=42)
+    ex = WaveExecutor(st, ds)
+    solver = BatchedSolver(ex, dag).plan()
+    funcs_per_level = {}
+    for w in solver.waves:
+        funcs_per_level.setdefault(w.level, set()).add(w.func)
+    assert any(len(f) == 2 for f in funcs_per_level.values())          # a level holding both kinds
+    assert any(w.copy_src for w in solver.waves if w.func == "train")  # shared model -> copied, not trained in place
+    res = solver.run()
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(32, 32, 3, 10)
+    sinks, _ = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=42, batch=32, local_steps=2, lr=0.002, mu=0.9, wd=0.0,
+                           n_i=n_i, minibatch_permutation=synthetic.minibatch_permutation)
+    assert sorted(res) == sorted(sinks) and len(sinks) >= 2
+    for name, row in sinks.items():
+        assert rel(res[name][0].numpy(), row[:L.P]) < 3e-4, name
+
+
 def test_functions_api_single_tasks(cuda, golden_dir, tmp_path):
     """The API-compatible entry points, one task per call like the reference worker: must give
     the same rows as the batched solver (same kernels, waves of one)."""

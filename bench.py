@@ -204,7 +204,7 @@ def run_reference(args):
                                        (sample, n_nodes, LOCAL_STEPS, BATCH, k + 1, procs, threads)},
             "e2e": {"value": value, "unit": "node-train-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(n_nodes, k, args):
@@ -223,8 +223,26 @@ def workload_config(n_nodes, k, args):
                                  "e2e uploads per-round task descriptors + minibatch index"}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """Print the ONE JSON line on the real stdout (library chatter such as NCCL's version banner is
+    sent to stderr by the fd redirection in main())."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                       # everything else that writes to fd 1 now goes to stderr
     if args.impl == "reference":
         return run_reference(args)
 
@@ -253,8 +271,6 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
 
@@ -417,7 +433,7 @@ def main():
                                               "(fan-in %d), 1 worker x 4 torch threads (reference defaults), "
                                               "%.1f s; host has %d cores" % (n_nodes, LOCAL_STEPS, BATCH, k + 1,
                                                                             secs, cores)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -277,7 +277,7 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
     }
     // a CTA serves a whole node when there are enough nodes to fill the GPU twice, else half a node
     int spc = p.gs;
-    if (p.n_groups < 2 * 148 && p.gs > SB) spc = ((p.gs / 2 + SB - 1) / SB) * SB;
+    if (p.n_groups < 148 && p.gs > SB) spc = ((p.gs / 2 + SB - 1) / SB) * SB;
     const int parts = (p.gs + spc - 1) / spc;
     conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * parts, CT_THREADS, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
                                                                                    bias_off, spc);

@@ -132,19 +132,24 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
         __syncthreads();
         tc::fence_after_sync();
         if (t == 0 && k + 2 < 8) issue(k + 2);
-        // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins)
-        const int py_lo = (k == 0) ? 0 : 2 * k - 1, n_py = (k == 0) ? 1 : 2;
-        for (int o = t; o < n_py * 15 * 32; o += C1F_THREADS) {
-            const int co = o / (n_py * 15), q = o - co * (n_py * 15), py = py_lo + q / 15, px = q % 15;
+        // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins).
+        // Index arithmetic uses compile-time divisors only (o -> channel, row 0/1, column).
+        for (int o = t; o < 32 * 30; o += C1F_THREADS) {
+            const int co = o / 30, q = o - co * 30, pr = q / 15, px = q - pr * 15;
+            const int py = 2 * k - 1 + pr;
+            if (py < 0) continue;
+            const float *rp = ring + co * 256 + 2 * px;
             float best = -INFINITY;
             int bi = 0;
 #pragma unroll
-            for (int dy = 0; dy < 3; ++dy)
+            for (int dy = 0; dy < 3; ++dy) {
+                const float *rr = rp + ((2 * py + dy) & 7) * 32;
 #pragma unroll
                 for (int dx = 0; dx < 3; ++dx) {
-                    const float v = ring[co * 256 + ((2 * py + dy) & 7) * 32 + 2 * px + dx];
+                    const float v = rr[dx];
                     if (v > best) { best = v; bi = dy * 3 + dx; }
                 }
+            }
             const int pp = py * 15 + px;
             ps[co * 225 + pp] = best;
             if (save_bwd) idx_out[pp * 32 + co] = (uint8_t)bi;

@@ -201,9 +201,9 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 constexpr int DC_PLANE = 1024 * 16;
 constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
 constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128;
-constexpr int C1W_THREADS = 256, C1W_PRODUCERS = 224;
+constexpr int C1W_THREADS = 512, C1W_PRODUCERS = 480;
 
-__device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 224;" ::: "memory"); }
+__device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 480;" ::: "memory"); }
 
 __global__ void __launch_bounds__(C1W_THREADS, 1)
 conv1_wgrad_tc_kernel(Pass p, Workspace ws)
@@ -260,7 +260,7 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
                 // read-modify-write below is race free within a pass and the sum order is fixed
                 // all global loads of the four passes are issued up front (registers), so that the passes
                 // themselves only touch shared memory between the producer barriers
-                constexpr int MAXIT = 10;                       // ceil(8*8*32 / 224)
+                constexpr int MAXIT = 5;                        // ceil(8*8*32 / 480)
                 float dv[4][MAXIT];
                 uint32_t cell[4][MAXIT];                        // byte offset of the bf16 cell, 0xffffffff = none
 #pragma unroll

@@ -655,11 +655,63 @@ int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *o
     return 0;
 }
 
+// The weight-gradient kernels only feed the optimizer, so in tensor-core mode they run on a side
+// stream next to the data-gradient chain (fork/join with events): with one CTA per node, 256 nodes
+// fill 1.73 waves of the 148 SMs, and the other stream's kernels use the SMs an unfinished wave
+// leaves idle.  The side stream is created once per device and joined before this call returns.
+struct SideStream { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
+static SideStream g_side[64];
+
+static int side_stream(SideStream **out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return DLS_E_TOO_BIG;
+    SideStream &ss = g_side[dev];
+    if (!ss.s) {
+        if ((e = cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+        if ((e = cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+        if ((e = cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+    }
+    *out = &ss;
+    return 0;
+}
+
+#define DLS_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return (int)e__; } while (0)
+
 int backward(const Pass &p, Workspace &ws, cudaStream_t st)
 {
     int rc = set_attrs();
     if (rc) return rc;
     const int S = p.n_groups * p.gs;
+    if (ws.precision == 1) {
+        SideStream *ss = nullptr;
+        if ((rc = side_stream(&ss))) return rc;
+        gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
+                                                              ws.gnp, p, OFF_G3W, 192);
+        DLS_LAUNCH_CHECK();
+        DLS_CUDA(cudaEventRecord(ss->fork, st));
+        DLS_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
+        if ((rc = conv3_wgrad_tc(p, ws, ss->s))) return rc;
+        if ((rc = conv3_dgrad_tc(p, ws, st))) return rc;
+        gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
+                                                               ws.gnp, p, OFF_G2W, 96);
+        DLS_LAUNCH_CHECK();
+        DLS_CUDA(cudaEventRecord(ss->fork, st));
+        DLS_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
+        if ((rc = conv2_wgrad_tc(p, ws, ss->s))) return rc;
+        if ((rc = conv2_dgrad_tc(p, ws, st))) return rc;
+        gn_block_bwd_kernel<32, 15, 15, false><<<S, 256, 0, st>>>(ws.da1, ws.a1, nullptr, ws.p1, ws.st1, ws.dp1,
+                                                                 ws.gnp, p, OFF_G1W, 0);
+        DLS_LAUNCH_CHECK();
+        if ((rc = conv1_wgrad_tc(p, ws, st))) return rc;
+        gn_param_reduce_kernel<<<p.n_groups, GNP_SZ, 0, st>>>(p, ws);
+        DLS_LAUNCH_CHECK();
+        DLS_CUDA(cudaEventRecord(ss->join, ss->s));
+        DLS_CUDA(cudaStreamWaitEvent(st, ss->join, 0));
+        return 0;
+    }
     // block 3
     gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
                                                           ws.gnp, p, OFF_G3W, 192);

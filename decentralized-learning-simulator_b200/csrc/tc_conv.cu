@@ -335,7 +335,10 @@ struct WgradTcCfg {
     static constexpr int CIN = 32;
     static constexpr int PP = H + 4;
     static constexpr int NPS = PP * PP;
-    static constexpr int KPIX = ((SB * NPS + 15) / 16) * 16;       // reduction length per chunk
+    // dY is zero at every origin past the last valid one of the chunk's last sample, so the reduction
+    // stops there (H=15, SB=1: 281 of the 361 padded positions -> 18 K steps instead of 23)
+    static constexpr int NVALID = (SB - 1) * NPS + (H - 1) * PP + H;
+    static constexpr int KPIX = ((NVALID + 1 + 15) / 16) * 16;     // reduction length per chunk (+1: shifted copy)
     static constexpr int TAIL = ((4 * PP + 4 + 7) / 8) * 8;
     static constexpr int NPD = KPIX, NPI = KPIX + TAIL;
     static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
@@ -359,7 +362,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws, int w_off)
 {
     using C = WgradTcCfg<COUT, H, SB, PAIR>;
-    static_assert(!PAIR || (C::NPD > SB * C::NPS), "pair trick needs a spare plane entry");
+    static_assert(!PAIR || (C::NPD > C::NVALID), "pair trick needs a spare plane entry");
+    static_assert(C::NPI >= SB * C::NPS, "input planes must hold every padded pixel of the chunk");
     static_assert(PAIR || COUT == 64, "without the pair trick the operand must have 64 real rows");
     constexpr int NMMA = PAIR ? 15 : C::TAPS0;           // accumulator tiles (32 columns each) per CTA
     extern __shared__ __align__(128) uint8_t smem[];
@@ -395,7 +399,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));   // MMAs of chunk c-2 done
             uint8_t *sD = smem + b * C::BUF;
             uint8_t *sI = sD + C::DPLANES * C::PLANE_D;
-            stage_items<8>(pt, SB * C::NPS * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
+            stage_items<8>(pt, C::NVALID * (COUT / 8), WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
                 const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
                 const int sl = c * SB + s;

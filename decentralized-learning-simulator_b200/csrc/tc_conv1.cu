@@ -58,7 +58,8 @@ __device__ __forceinline__ void build_expanded(const uint8_t *simg, const __nv_b
     }
 }
 
-constexpr int C1F_SMEM = 2 * E_PLANE + C1_W_BYTES + 32 * 256 * 4 + 32 * 225 * 4 + 3072 + 512 + 32 * 4 + 32 * 4 + 64;
+constexpr int RING_FLOATS = 8 * 32 * 33;       // conv rows ring: [8 rows][32 ox][32 co + 1 pad]
+constexpr int C1F_SMEM = 2 * E_PLANE + C1_W_BYTES + RING_FLOATS * 4 + 32 * 225 * 4 + 3072 + 512 + 32 * 4 + 32 * 4 + 64;
 
 constexpr int C1F_THREADS = 256;      // warps 0-3 drain TMEM; all warps expand the image, pool and normalise
 
@@ -68,8 +69,8 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *sE = smem;
     uint8_t *sW = sE + 2 * E_PLANE;
-    float *ring = reinterpret_cast<float *>(sW + C1_W_BYTES);        // [32 co][8 rows][32 ox]
-    float *ps = ring + 32 * 256;                                      // [32 co][225]
+    float *ring = reinterpret_cast<float *>(sW + C1_W_BYTES);        // [8 rows][32 ox][33]: channel fastest, padded
+    float *ps = ring + RING_FLOATS;                                      // [32 co][225]
     uint8_t *simg = reinterpret_cast<uint8_t *>(ps + 32 * 225);
     __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
     float *sbias = reinterpret_cast<float *>(simg + 3072 + 512);
@@ -124,35 +125,46 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
             tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((k & 1) * 32), r);
             tc::tmem_ld_wait();
             // thread t holds conv output pixel (row 4k + t/32, ox = t%32), 32 channels
-            const int rr = ((4 * k + (t >> 5)) & 7) * 32 + (t & 31);
+            float *rw = ring + (((4 * k + (t >> 5)) & 7) * 32 + (t & 31)) * 33;     // stride 33: conflict free
 #pragma unroll
-            for (int co = 0; co < 32; ++co) ring[co * 256 + rr] = __uint_as_float(r[co]) + sbias[co];
+            for (int co = 0; co < 32; ++co) rw[co] = __uint_as_float(r[co]) + sbias[co];
         }
         tc::fence_before_sync();
         __syncthreads();
         tc::fence_after_sync();
         if (t == 0 && k + 2 < 8) issue(k + 2);
         // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins).
-        // Index arithmetic uses compile-time divisors only (o -> channel, row 0/1, column).
-        for (int o = t; o < 32 * 30; o += C1F_THREADS) {
-            const int co = o / 30, q = o - co * 30, pr = q / 15, px = q - pr * 15;
+        // lane = channel; warp = (pooled row 0/1, quarter of the 15 columns): a thread loads the 3 x 9
+        // conv values its (up to) four adjacent windows share and scans each window in (dy, dx) order.
+        {
+            const int co = t & 31, pr = warp >> 2, qd = warp & 3, px0 = qd * 4, npx = (qd == 3) ? 3 : 4;
             const int py = 2 * k - 1 + pr;
-            if (py < 0) continue;
-            const float *rp = ring + co * 256 + 2 * px;
-            float best = -INFINITY;
-            int bi = 0;
+            if (py >= 0) {
+                float v[3][9];
 #pragma unroll
-            for (int dy = 0; dy < 3; ++dy) {
-                const float *rr = rp + ((2 * py + dy) & 7) * 32;
+                for (int dy = 0; dy < 3; ++dy) {
+                    const float *rr = ring + ((((2 * py + dy) & 7) * 32 + 2 * px0) * 33) + co;
 #pragma unroll
-                for (int dx = 0; dx < 3; ++dx) {
-                    const float v = rr[dx];
-                    if (v > best) { best = v; bi = dy * 3 + dx; }
+                    for (int x = 0; x < 9; ++x) v[dy][x] = (x <= 2 * npx) ? rr[x * 33] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (j < npx) {
+                        float best = -INFINITY;
+                        int bi = 0;
+#pragma unroll
+                        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                            for (int dx = 0; dx < 3; ++dx) {
+                                const float x = v[dy][2 * j + dx];
+                                if (x > best) { best = x; bi = dy * 3 + dx; }
+                            }
+                        const int pp = py * 15 + px0 + j;
+                        ps[co * 225 + pp] = best;
+                        if (save_bwd) idx_out[pp * 32 + co] = (uint8_t)bi;
+                    }
                 }
             }
-            const int pp = py * 15 + px;
-            ps[co * 225 + pp] = best;
-            if (save_bwd) idx_out[pp * 32 + co] = (uint8_t)bi;
         }
         __syncthreads();
     }

@@ -35,26 +35,44 @@ prep_w1_tc_kernel(Pass p, __nv_bfloat16 *prep, const int32_t *model_active)
     }
 }
 
-// Build the x-expanded bf16 planes of one image from its raw uint8 HWC bytes (in shared memory).
-__device__ __forceinline__ void build_expanded(const uint8_t *simg, const __nv_bfloat16 *lut, uint8_t *sE, int t,
-                                               int nthreads)
+// The image is first converted once to bf16 rows in shared memory, padded like the convolution
+// (2 zero pixels left, >= 2 right): row[6 + x*3 + c] = bf16(byte / 255).
+constexpr int ROW16 = 116;                       // bf16 elements per padded row (58 32-bit words)
+constexpr int S16_BYTES = 32 * ROW16 * 2;
+
+__device__ __forceinline__ void convert_rows(const uint8_t *simg, const __nv_bfloat16 *lut, uint32_t *s16, int t,
+                                             int nthreads)
+{
+    for (int i = t; i < 32 * (ROW16 / 2); i += nthreads) {
+        const int row = i / (ROW16 / 2), w = i - row * (ROW16 / 2), e0 = 2 * w - 6;
+        const uint8_t *rp = simg + row * 96;
+        const uint32_t lo = (e0 >= 0 && e0 < 96) ? __bfloat16_as_ushort(lut[rp[e0]]) : 0u;
+        const uint32_t hi = (e0 + 1 >= 0 && e0 + 1 < 96) ? __bfloat16_as_ushort(lut[rp[e0 + 1]]) : 0u;
+        s16[i] = lo | (hi << 16);
+    }
+}
+
+// Build the x-expanded bf16 planes E[j][py][ox][8] from the padded bf16 rows: entry (py, ox, j) is the
+// eight consecutive row elements starting at ox*3 + 8j (the 16th element of a pixel is a zero pad).
+__device__ __forceinline__ void build_expanded(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
 {
     for (int i = t; i < 36 * 32 * 2; i += nthreads) {
         const int j = i & 1, ox = (i >> 1) & 31, py = i >> 6;
         const int y = py - 2;
-        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (y >= 0 && y < 32) {
-            const int b0 = (ox - 2) * 3 + 8 * j;
-            const uint8_t *rowp = simg + y * 96;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int bi = b0 + e;
-                unsigned short h = 0;
-                if (bi >= 0 && bi < 96 && 8 * j + e < 15) h = __bfloat16_as_ushort(lut[rowp[bi]]);
-                w[e >> 1] |= (uint32_t)h << ((e & 1) * 16);
+            const int off = ox * 3 + 8 * j;
+            const uint32_t *rw = s16 + y * (ROW16 / 2) + (off >> 1);
+            const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
+            if (off & 1) {
+                v.x = __funnelshift_r(w0, w1, 16); v.y = __funnelshift_r(w1, w2, 16);
+                v.z = __funnelshift_r(w2, w3, 16); v.w = __funnelshift_r(w3, w4, 16);
+            } else {
+                v.x = w0; v.y = w1; v.z = w2; v.w = w3;
             }
+            if (j) v.w &= 0x0000FFFFu;           // element 15 of the (kx, c) vector is the zero pad
         }
-        *reinterpret_cast<uint4 *>(sE + j * E_PLANE + (py * 32 + ox) * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4 *>(sE + j * E_PLANE + (py * 32 + ox) * 16) = v;
     }
 }
 
@@ -77,6 +95,7 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
     float *red = sbias + 32;
     uint64_t *bars = reinterpret_cast<uint64_t *>(red + 32);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
+    uint32_t *s16 = reinterpret_cast<uint32_t *>(ring);      // bf16 image rows; dead before the ring is first written
 
     const int slot = blockIdx.x, t = threadIdx.x, warp = t >> 5;
     const int id = p.img_idx[slot];
@@ -97,7 +116,9 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
     if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 64);
     __syncthreads();
-    build_expanded(simg, lut, sE, t, C1F_THREADS);
+    convert_rows(simg, lut, s16, t, C1F_THREADS);
+    __syncthreads();
+    build_expanded(s16, sE, t, C1F_THREADS);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -212,7 +233,7 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 // ------------------------------------------------------------------------------------------
 constexpr int DC_PLANE = 1024 * 16;
 constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
-constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128;
+constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128 + S16_BYTES;
 constexpr int C1W_THREADS = 512, C1W_PRODUCERS = 480;
 
 __device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 480;" ::: "memory"); }
@@ -225,6 +246,7 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
     __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
     uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 3072 + 512);       // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
+    uint32_t *s16 = reinterpret_cast<uint32_t *>(simg + 3072 + 512 + 128);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int g = blockIdx.x, gs = p.gs;
     if (p.gcount[g] <= 0) return;
@@ -265,7 +287,9 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
             }
             producer_sync();
             if (id >= 0) {
-                build_expanded(simg, lut, sE, pt, C1W_PRODUCERS);
+                convert_rows(simg, lut, s16, pt, C1W_PRODUCERS);
+                producer_sync();
+                build_expanded(s16, sE, pt, C1W_PRODUCERS);
                 const float *dp = ws.dp1 + (int64_t)slot * A1_SZ;
                 const uint8_t *ix = ws.idx1 + (int64_t)slot * A1_SZ;
                 // windows of one colour (py%2, px%2) never touch the same conv position, so the

@@ -112,8 +112,30 @@ class WaveExecutor:
         if self.refs[slot] == 0:
             self.free.append(slot)
 
+    def _upload(self, *arrays) -> List[torch.Tensor]:
+        """One asynchronous host->device copy for several small descriptor arrays: they are packed
+        into one pinned staging block (torch's caching host allocator keeps the block alive until the
+        copy has run), so the host never waits for kernels queued on the stream — a pageable
+        cudaMemcpyAsync would."""
+        arrs = [np.ascontiguousarray(a) for a in arrays]
+        if self.device.type != "cuda":
+            return [torch.from_numpy(a.copy()) for a in arrs]
+        offs, n = [], 0
+        for a in arrs:
+            offs.append(n)
+            n += (a.nbytes + 15) & ~15
+        host = torch.empty(max(n, 16), dtype=torch.uint8, pin_memory=True)
+        hv = host.numpy()
+        for a, o in zip(arrs, offs):
+            hv[o:o + a.nbytes] = a.reshape(-1).view(np.uint8)
+        dev = host.to(self.device, non_blocking=True)
+        out = []
+        for a, o in zip(arrs, offs):
+            out.append(dev[o:o + a.nbytes].view(getattr(torch, a.dtype.name)).reshape(a.shape))
+        return out
+
     def _dev_i32(self, a) -> torch.Tensor:
-        return torch.as_tensor(np.ascontiguousarray(a, dtype=np.int32)).to(self.device, non_blocking=True)
+        return self._upload(np.asarray(a, dtype=np.int32))[0]
 
     # -- waves ------------------------------------------------------------------------------
     def init_rows(self, slots: Sequence[int]):
@@ -139,8 +161,9 @@ class WaveExecutor:
         if len(set(local)) != len(local):
             raise DlsError("a train wave holds two tasks of the same node; they must run in different waves")
         first = np.array([0 if self.mom_valid[l] else 1 for l in local], dtype=np.uint8)
-        K.train_wave(self.layout, self.X, self.M, self._dev_i32(slots), self._dev_i32(local),
-                     torch.from_numpy(first).to(self.device, non_blocking=True), self.dataset.images,
+        d_slots, d_local, d_first = self._upload(np.asarray(slots, dtype=np.int32),
+                                                 np.asarray(local, dtype=np.int32), first)
+        K.train_wave(self.layout, self.X, self.M, d_slots, d_local, d_first, self.dataset.images,
                      self.dataset.labels, mb_index, mb_count, int(ls.batch_size), float(ls.learning_rate),
                      float(ls.momentum), float(ls.weight_decay), self.ws, loss_out=loss_out,
                      precision=self.precision)
@@ -157,12 +180,8 @@ class WaveExecutor:
         steps = list(steps) if steps is not None else [int(ls.local_steps)] * len(peers)
         idx, cnt = self.dataset.minibatches(peers, rounds, int(ls.batch_size), steps)
         done = (cnt > 0).sum(axis=0).tolist()
-        pin = torch.cuda.is_available()
-        ti = torch.from_numpy(idx)
-        tc = torch.from_numpy(cnt)
-        if pin:
-            ti, tc = ti.pin_memory(), tc.pin_memory()
-        return ti.to(self.device, non_blocking=True), tc.to(self.device, non_blocking=True), done
+        ti, tc = self._upload(idx, cnt)
+        return ti, tc, done
 
     def aggregate_wave(self, model_slots: Sequence[Sequence[int]], out_slots: Sequence[int],
                        weights: Optional[Sequence[Optional[Sequence[float]]]] = None, variant: int = 0,
@@ -211,11 +230,10 @@ class WaveExecutor:
         fans = np.diff(rowptr)
         uniform = len(fans) > 0 and int(fans.min()) == int(fans.max()) and 2 <= int(fans[0]) <= 16
         hint = {"order": ([3] if uniform else []) + [2, 1]}
-        return (torch.from_numpy(rowptr).to(dev, non_blocking=True),
-                torch.from_numpy(np.asarray(col, dtype=np.int32)).to(dev, non_blocking=True),
-                torch.from_numpy(np.asarray(w, dtype=np.float64).astype(np.float32)).to(dev, non_blocking=True),
-                torch.from_numpy(src_rows).to(dev, non_blocking=True),
-                self._dev_i32(out_slots), len(src_index), hint)
+        up = self._upload(rowptr, np.asarray(col, dtype=np.int32),
+                          np.asarray(w, dtype=np.float64).astype(np.float32), src_rows,
+                          np.asarray(out_slots, dtype=np.int32))
+        return (*up, len(src_index), hint)
 
     def test_wave(self, slots: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
         """(accuracy %, mean loss) per slot on the whole test split

@@ -145,31 +145,34 @@ class DistributedSolver(BatchedSolver):
     def _model_slot(self, ref):
         if ref in self._value_slot:
             return self._value_slot[ref]
-        return -1 - self._halo_of[ref]                        # halo row, fixed up in _finish_plan
+        return -1 - self._halo_of[ref]                        # halo row, fixed up in _fixup_wave
 
     def _end_level_wave(self, level: int, wave: Wave):
         if wave.func == "aggregate" and level in self._level_xchg:
             wave.xchg = self._level_xchg[level]
 
-    def _finish_plan(self, extra_slots: int):
+    def _level_waves(self, level: int, waves: List[Wave]) -> List[Wave]:
+        # a level where this rank only sends (it owns no aggregate there) still takes part in the exchange
+        x = self._level_xchg.get(level)
+        if x is not None and not any(getattr(w, "xchg", None) for w in waves):
+            w = Wave(level, "exchange")
+            w.xchg = x
+            waves = waves + [w]
+        return waves
+
+    def _grow_pool(self, extra_slots: int):
+        self.ex._grow(extra_slots, halo_rows=self.max_halo, send_rows=self.max_send)
+
+    def _fixup_wave(self, w: Wave):
+        """Halo references become rows after the pool (valid once the pool has its planned size)."""
         ex = self.ex
-        ex._grow(extra_slots, halo_rows=self.max_halo, send_rows=self.max_send)
         base = ex.halo_base
-        # levels where this rank only sends (it owns no aggregate there) still take part in the exchange
-        have = {w.level for w in self.waves if getattr(w, "xchg", None)}
-        for level, x in self._level_xchg.items():
-            if level not in have:
-                w = Wave(level, "exchange")
-                w.xchg = x
-                pos = next((i for i, ww in enumerate(self.waves) if ww.level > level), len(self.waves))
-                self.waves.insert(pos, w)
-        for w in self.waves:
-            if w.func == "aggregate":
-                w.model_slots = [[s if s >= 0 else base + (-1 - s) for s in ms] for ms in w.model_slots]
-            x = getattr(w, "xchg", None)
-            if x:
-                x["send_idx"] = ex._dev_i32(x["send_slots"]) if x["send_slots"] else None
-                self.halo_bytes += sum(x["recv_counts"]) * ex.layout.P * 4
+        if w.func == "aggregate":
+            w.model_slots = [[s if s >= 0 else base + (-1 - s) for s in ms] for ms in w.model_slots]
+        x = getattr(w, "xchg", None)
+        if x and "send_idx" not in x:
+            x["send_idx"] = ex._dev_i32(x["send_slots"]) if x["send_slots"] else None
+            self.halo_bytes += sum(x["recv_counts"]) * ex.layout.P * 4
 
     # -- execution --------------------------------------------------------------------------
     def exchange(self, x: dict):

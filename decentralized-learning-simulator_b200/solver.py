@@ -9,7 +9,9 @@ levelises the DAG into wavefronts, groups every wavefront by task function and r
 as ONE batched GPU wave on rows of the stacked parameter tensor.
 
 `plan()` does all host-side work once (levelisation, slot assignment with reference counts,
-CSR construction, minibatch index); `run()` then only uploads per-wave descriptors and launches.
+CSR construction, minibatch index); `run()` then only launches.  Without a prior `plan()`,
+`run()` / `run_with_loss()` stream the graph: level k+1 is planned on the host while level k
+executes on the GPU, so only the first level's planning is exposed.
 """
 from collections import defaultdict
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
@@ -103,7 +105,9 @@ class BatchedSolver:
                                % (seen, len(self.tasks)))
         return levels
 
-    def plan(self):
+    def _plan_levels(self):
+        """Generator: assigns slots for one wavefront at a time and yields that level's waves.
+        Nothing touches the device here; `_commit` does (pool growth, descriptor upload)."""
         ex = self.ex
         ls = ex.settings.learning
         value_slot: Dict[Tuple[str, int], int] = {}
@@ -111,22 +115,16 @@ class BatchedSolver:
         for s_live in np.nonzero(ex.refs)[0]:
             sim_refs[int(s_live)] = int(ex.refs[s_live])
         free: List[int] = list(ex.free)
-        n_slots = ex.n_slots
-        extra = 0
+        self._planned_slots = ex.n_slots
+        self._plan_free, self._plan_refs = free, sim_refs
+        tasks, owned, initial = self.tasks, self.owned, self.initial_models
+        default_steps = int(ls.local_steps)
 
         def take() -> int:
-            nonlocal extra, n_slots
             if not free:
-                free.append(n_slots)
-                n_slots += 1
-                extra += 1
+                free.append(self._planned_slots)
+                self._planned_slots += 1
             return free.pop()
-
-        def drop(slot: int):
-            sim_refs[slot] -= 1
-            assert sim_refs[slot] >= 0
-            if sim_refs[slot] == 0:
-                free.append(slot)
 
         self._value_slot = value_slot
         for li, names in enumerate(self.levelise()):
@@ -135,26 +133,28 @@ class BatchedSolver:
             pending_release: List[int] = []
             self._begin_level(li, names, pending_release)
             for name in names:
-                t = self.tasks[name]
+                t = tasks[name]
                 d = t["data"]
-                if self.owned is not None and int(d["peer"]) not in self.owned:
+                peer = int(d["peer"])
+                if owned is not None and peer not in owned:
                     continue
-                w = by_func.get(t["func"])
+                func = t["func"]
+                w = by_func.get(func)
                 if w is None:
-                    w = by_func[t["func"]] = Wave(li, t["func"])
+                    w = by_func[func] = Wave(li, func)
                 n_cons = len(t["outputs"])
                 keep = n_cons if n_cons > 0 else 1          # sinks keep their row as the result
                 w.names.append(name)
-                w.peers.append(int(d["peer"]))
+                w.peers.append(peer)
                 w.rounds.append(int(d.get("round", 0)))
                 w.times.append(int(d.get("time", 0)))
-                if t["func"] == "train":
+                if func == "train":
                     src = d["model"]
                     if isinstance(src, tuple) and src[0] is None:
                         src = None
-                    w.steps.append(int(d.get("local_steps", ls.local_steps)))
-                    if src is None and int(d["peer"]) in self.initial_models:
-                        slot = self.initial_models[int(d["peer"])]      # resume: train in place
+                    w.steps.append(int(d.get("local_steps", default_steps)))
+                    if src is None and peer in initial:
+                        slot = initial[peer]                 # resume: train in place
                         sim_refs[slot] -= 1
                     elif src is None:                        # first round: (None, 0)
                         slot = take()
@@ -173,7 +173,7 @@ class BatchedSolver:
                     w.out_slots.append(slot)
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
-                elif t["func"] == "aggregate":
+                elif func == "aggregate":
                     ms = [self._model_slot(tuple(m)) for m in d["models"]]
                     slot = take()
                     w.model_slots.append(ms)
@@ -193,24 +193,53 @@ class BatchedSolver:
                     self.sink_slots[name] = value_slot[(name, 0)]
             # inputs are released only after the whole level ran (their rows are read by this level)
             for s in pending_release:
-                drop(s)
-            order = [f for f in ("train", "aggregate", "test") if f in by_func]
-            for f in order:
-                self._end_level_wave(li, by_func[f])
-                self.waves.append(by_func[f])
-        self._finish_plan(extra)
-        # host->device descriptors
-        for w in self.waves:
-            if w.func == "train":
-                w.prepared = ex.prepare_train(w.peers, w.rounds, w.steps)
-                self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:2] if hasattr(t, 'numel'))
-            elif w.func == "aggregate":
-                w.prepared = ex.prepare_aggregate(w.model_slots, w.out_slots, w.weights)
-                self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:5] if hasattr(t, 'numel'))
-        self._plan_free = free
-        self._plan_refs = dict(sim_refs)
+                n = sim_refs[s] - 1
+                assert n >= 0
+                sim_refs[s] = n
+                if n == 0:
+                    free.append(s)
+            level_waves = [by_func[f] for f in ("train", "aggregate", "test") if f in by_func]
+            for w in level_waves:
+                self._end_level_wave(li, w)
+            yield self._level_waves(li, level_waves)
+
+    def plan(self):
+        """Whole-graph planning: every level's slots and descriptors before the first launch."""
+        for level_waves in self._plan_levels():
+            self.waves.extend(level_waves)
+        self._commit(self.waves)
         self.planned = True
         return self
+
+    def _commit(self, waves: List[Wave]):
+        """Device side of planning for `waves`: grow the pool to the planned size, then upload
+        the wave descriptors (pinned staging, asynchronous)."""
+        self._grow_pool(self._planned_slots - self.ex.n_slots)
+        for w in waves:
+            self._fixup_wave(w)
+            self._prepare(w)
+
+    def _prepare(self, w: Wave):
+        ex = self.ex
+        if w.func == "train":
+            w.prepared = ex.prepare_train(w.peers, w.rounds, w.steps)
+            self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:2] if hasattr(t, 'numel'))
+        elif w.func == "aggregate":
+            w.prepared = ex.prepare_aggregate(w.model_slots, w.out_slots, w.weights)
+            self.h2d_bytes += sum(t.numel() * t.element_size() for t in w.prepared[:5] if hasattr(t, 'numel'))
+
+    def _stream(self):
+        """Waves in execution order.  Unplanned solvers plan level k+1 on the host while level k
+        runs on the GPU (launches and descriptor uploads are asynchronous)."""
+        if self.planned:
+            yield from self.waves
+            return
+        for level_waves in self._plan_levels():
+            self._commit(level_waves)
+            for w in level_waves:
+                self.waves.append(w)
+                yield w
+        self.planned = True
 
     # hooks overridden by the multi-GPU solver (partition.DistributedSolver)
     def _begin_level(self, level: int, names: List[str], pending_release: List[int]):
@@ -222,9 +251,15 @@ class BatchedSolver:
     def _end_level_wave(self, level: int, wave: Wave):
         pass
 
-    def _finish_plan(self, extra_slots: int):
+    def _level_waves(self, level: int, waves: List[Wave]) -> List[Wave]:
+        return waves
+
+    def _grow_pool(self, extra_slots: int):
         if extra_slots:
             self.ex._grow(extra_slots)
+
+    def _fixup_wave(self, wave: Wave):
+        pass
 
     # -- execution --------------------------------------------------------------------------
     def run_wave(self, w: Wave, loss_out=None):
@@ -251,11 +286,9 @@ class BatchedSolver:
                 ex.refs[s] = n
 
     def run(self, timing: bool = False):
-        if not self.planned:
-            self.plan()
         ex = self.ex
         results: Dict[str, List[RowHandle]] = {}
-        for w in self.waves:
+        for w in self._stream():
             if timing:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
@@ -278,10 +311,8 @@ class BatchedSolver:
     def run_with_loss(self):
         """Run all waves; returns the device tensor `[steps, n_tasks]` of mean minibatch losses of
         the last train wave (the step result a caller reads back)."""
-        if not self.planned:
-            self.plan()
         loss = None
-        for w in self.waves:
+        for w in self._stream():
             if w.func == "train":
                 loss = torch.zeros((max(w.steps), len(w.names)), dtype=torch.float32, device=self.ex.device)
                 self.run_wave(w, loss_out=loss)

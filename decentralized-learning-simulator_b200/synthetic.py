@@ -42,11 +42,15 @@ def make_test_split(n_test: int, hw: int, c: int, num_classes: int, seed: int = 
     return img, labels
 
 
+_U30, _U27, _U31 = np.uint64(30), np.uint64(27), np.uint64(31)
+_M1, _M2 = np.uint64(0xBF58476D1CE4E5B9), np.uint64(0x94D049BB133111EB)
+
+
 def _mix64(x: np.ndarray) -> np.ndarray:
     """splitmix64 finaliser (vectorised, wraps modulo 2^64)."""
-    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
-    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
-    return x ^ (x >> np.uint64(31))
+    x = (x ^ (x >> _U30)) * _M1
+    x = (x ^ (x >> _U27)) * _M2
+    return x ^ (x >> _U31)
 
 
 def minibatch_permutations(seed: int, nodes: Sequence[int], rounds: Sequence[int], n_i: int) -> np.ndarray:
@@ -62,9 +66,13 @@ def minibatch_permutations(seed: int, nodes: Sequence[int], rounds: Sequence[int
         idx = np.arange(n_i, dtype=np.uint64).reshape(1, -1)
         keys = _mix64(base + idx * np.uint64(0x9E3779B97F4A7C15))
         # the sample index in the low 24 bits makes every key unique, so the order does not depend on
-        # the sort algorithm (and the default introsort / SIMD sort can be used)
-        keys = (keys & np.uint64(0xFFFFFFFFFF000000)) | idx
-    return np.argsort(keys, axis=1).astype(np.int32)
+        # the sort algorithm, and sorting the keys themselves (cheaper than an argsort) yields the
+        # permutation in their low bits
+        keys &= np.uint64(0xFFFFFFFFFF000000)
+        keys |= idx
+        keys.sort(axis=1)
+        keys &= np.uint64(0xFFFFFF)
+    return keys.astype(np.int32)
 
 
 def minibatch_permutation(seed: int, node: int, round_nr: int, n_i: int) -> np.ndarray:

@@ -198,3 +198,39 @@ def test_c2_two_rounds_properties(cuda, golden_dir, tmp_path):
     spread = (finals[0] - finals[0].mean(0)).norm(dim=1).mean()
     moved = (finals[0].mean(0) - init).norm()
     assert float(moved) > 0 and float(spread) < float(moved)        # consensus distance << progress
+
+
+@pytest.mark.parametrize("precision", [0, 1])
+def test_streamed_solve_equals_planned_solve(cuda, golden_dir, tmp_path, precision):
+    """`run()` without a prior `plan()` plans level k+1 while level k executes; slots, waves and
+    every output bit are those of the fully planned solve, also when continuing from seeded models."""
+    g, meta, dag, st, ds = mini(golden_dir, tmp_path, cuda)
+    st.precision = precision
+    out = []
+    for streamed in (False, True):
+        ex = WaveExecutor(st, ds, n_slots=4)                       # small pool: growth happens mid-stream
+        solver = BatchedSolver(ex, dag)
+        if not streamed:
+            solver.plan()
+        res = solver.run()
+        rows = {name: h[0].numpy().copy() for name, h in res.items()}
+        # a second graph (one more round) continuing from the models left in HBM
+        nxt = synthetic.dpsgd_dag(meta["n"], 1, synthetic.kreg_topology(meta["n"], 2, seed=7), name_offset=1000)
+        s2 = BatchedSolver(ex, nxt).seed_models(solver.final_slots())
+        if not streamed:
+            s2.plan()
+        loss = s2.run_with_loss()
+        rows2 = {name: RowHandleNumpy(ex, slot) for name, slot in s2.sink_slots.items()}
+        out.append((rows, rows2, loss.cpu().numpy(), [(w.func, w.out_slots) for w in solver.waves + s2.waves]))
+    (r_a, r2_a, l_a, w_a), (r_b, r2_b, l_b, w_b) = out
+    assert w_a == w_b
+    assert sorted(r_a) == sorted(r_b) and sorted(r2_a) == sorted(r2_b)
+    for k in r_a:
+        assert np.array_equal(r_a[k].view(np.uint32), r_b[k].view(np.uint32))
+    for k in r2_a:
+        assert np.array_equal(r2_a[k].view(np.uint32), r2_b[k].view(np.uint32))
+    assert np.array_equal(l_a.view(np.uint32), l_b.view(np.uint32))
+
+
+def RowHandleNumpy(ex, slot):
+    return ex.X[slot, :ex.layout.P].cpu().numpy().copy()

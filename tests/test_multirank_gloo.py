@@ -34,7 +34,7 @@ def _dag():
     return synthetic.dpsgd_dag(N, ROUNDS, nb, test_interval=ROUNDS, order_seed=5), nb
 
 
-def _worker(rank, world, port, tmp, owner, out_q):
+def _worker(rank, world, port, tmp, owner, out_q, streamed=False):
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     from cpu_standin import OracleExecutor
     torch.set_num_threads(1)
@@ -44,8 +44,10 @@ def _worker(rank, world, port, tmp, owner, out_q):
     timg, tlab = synthetic.make_test_split(N_TEST, 32, 3, 10)
     owned = [int(p) for p in np.nonzero(np.asarray(owner) == rank)[0]]
     ex = OracleExecutor(_settings(tmp), imgs, labs, timg, tlab, owned, N_I)
-    solver = DistributedSolver(ex, dag, rank, world, owner).plan()
-    res = solver.run()
+    solver = DistributedSolver(ex, dag, rank, world, owner)
+    if not streamed:
+        solver.plan()
+    res = solver.run()              # unplanned: levels are planned, committed and exchanged one at a time
     out = {name: h[0].executor.X[h[0].slot, :L.P].numpy().copy() for name, h in res.items()}
     out_q.put((rank, out, solver.halo_bytes, solver.max_halo, solver.max_send))
     dist.barrier()
@@ -62,7 +64,8 @@ def test_two_ranks_equal_single_process_oracle(tmp_path, how):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, str(tmp_path), owner.tolist(), q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, str(tmp_path), owner.tolist(), q, how == "bfs"))
+             for r in range(2)]
     for p in procs:
         p.start()
     got = {}

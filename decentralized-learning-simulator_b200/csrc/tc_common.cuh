@@ -37,6 +37,16 @@ __device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence
 // make generic-proxy shared-memory writes visible to the async proxy (tcgen05.mma operand reads)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Warp index the compiler can prove warp-uniform (threadIdx.x >> 5 alone is treated as divergent, and
+// every tcgen05 instruction under a divergent branch is wrapped in an ELECT/BRA.U.ANY waterfall loop).
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+// One lane of a converged warp.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- MMA (kind::f16: bf16/fp16 operands, fp32 accumulate), issued by ONE thread ----
 __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                         uint32_t accumulate) {

@@ -95,13 +95,32 @@ __device__ __forceinline__ void stage_items(int first, int n_items, int stride, 
     }
 }
 
+// Padded plane geometry.  The pads are SHARED: a row's two right pad pixels are the next row's two left
+// pad pixels (pitch H + 2), and a sample's two bottom pad rows are the next sample's two top pad rows
+// (sample stride (H + 2) rows).  All pads are zero, so every shifted window still reads zeros outside
+// the image, while the origins (window top-left corners) of a sample shrink from (H+4)^2 to (H-1)*PP + H:
+// 253 for H = 15 — two M = 128 tiles per sample — and 61 for H = 7.
+template <int H>
+struct PlaneGeom {
+    static constexpr int PP = H + 2;                       // row pitch
+    static constexpr int NPS = (H + 2) * PP;               // sample stride (pixels)
+    static constexpr int NORIG = (H - 1) * PP + H;         // origins of one sample
+    static constexpr int EXTENT = (H + 4) * PP + 2;        // pixels a sample's windows can touch
+    static constexpr int TAIL = 4 * PP + 4;                // furthest tap shift
+};
+
 template <int CIN, int COUT, int H, int SB>
 struct ConvTcCfg {
-    static constexpr int PP = H + 4;
-    static constexpr int NPS = PP * PP;                    // padded pixels per sample
-    static constexpr int LAST = (H - 1) * PP + H;          // origins needed in the last sample
-    static constexpr int TAIL = 4 * PP + 4;                // furthest tap shift
-    static constexpr int NPIX = ((SB * NPS + TAIL + 128 + 7) / 8) * 8;   // + one tile of slack for the last M tile
+    using G = PlaneGeom<H>;
+    static constexpr int PP = G::PP, NPS = G::NPS, NORIG = G::NORIG, TAIL = G::TAIL;
+    // M tiles of a chunk: either every sample gets its own ceil(NORIG / 128) tiles, or the chunk's origins
+    // are enumerated contiguously across samples — whichever needs fewer tiles
+    static constexpr int TPS = (NORIG + 127) / 128;
+    static constexpr int TILES_GLOBAL = ((SB - 1) * NPS + NORIG + 127) / 128;
+    static constexpr bool PER_SAMPLE = SB * TPS <= TILES_GLOBAL;
+    static constexpr int REACH = PER_SAMPLE ? (SB - 1) * NPS + TPS * 128 + TAIL : TILES_GLOBAL * 128 + TAIL;
+    static constexpr int FULL = (SB - 1) * NPS + G::EXTENT;
+    static constexpr int NPIX = (((REACH > FULL ? REACH : FULL) + 7) / 8) * 8;
     static constexpr int PLANE = NPIX * 16;                // bytes
     static constexpr int NCH = CIN / 8;
     static constexpr int KCH = 25 * NCH;                   // 8-element K chunks
@@ -109,6 +128,12 @@ struct ConvTcCfg {
     static constexpr int A_BYTES = NCH * PLANE;
     static constexpr int SMEM = B_BYTES + 2 * A_BYTES + COUT * 4 + 128;
     static constexpr int TMEM_COLS = (2 * COUT <= 64) ? 64 : 128;
+    __host__ __device__ static constexpr int tiles(int ns) {
+        return PER_SAMPLE ? ns * TPS : ((ns - 1) * NPS + NORIG + 127) / 128;
+    }
+    __host__ __device__ static constexpr int tile_start(int tile) {      // first origin (pixel index) of a tile
+        return PER_SAMPLE ? (tile / TPS) * NPS + (tile % TPS) * 128 : tile * 128;
+    }
 };
 
 // Warp-specialised, persistent over the samples of a node (or half a node):
@@ -133,7 +158,7 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     uint64_t *bars = reinterpret_cast<uint64_t *>(sbias + COUT);       // full[2] empty[2] tfull[2] tempty[2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
 
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int parts = (p.gs + spc - 1) / spc;
     const int g = blockIdx.x / parts, part = blockIdx.x - g * parts;
     if (p.gcount[g] <= 0) return;
@@ -171,7 +196,7 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     const uint32_t tmem = *tmem_slot;
 
     auto chunk_samples = [&](int c) { const int r = (s_end - s_begin) - c * SB; return r < SB ? r : SB; };
-    auto chunk_tiles = [&](int c) { return ((chunk_samples(c) - 1) * C::NPS + C::LAST + 127) / 128; };
+    auto chunk_tiles = [&](int c) { return C::tiles(chunk_samples(c)); };
 
     if (warp >= 5) {
         // ------------------------------ producers ------------------------------
@@ -192,21 +217,23 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
         }
     } else if (warp == 4) {
         // ------------------------------ MMA issuer ------------------------------
-        if (lane == 0) {
-            const uint32_t idesc = tc::instr_desc_bf16(128, COUT, 0, 0);
-            const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sB), COUT * 16, 128);
-            int gt = 0;
-            for (int c = 0; c < n_chunks; ++c) {
-                const int b = c & 1;
-                tc::mbar_wait(&bars[b], (uint32_t)((c >> 1) & 1));
-                tc::fence_after_sync();
-                const uint32_t a_base = tc::smem_u32(sA0 + b * C::A_BYTES);
-                const int nt = chunk_tiles(c);
-                for (int tile = 0; tile < nt; ++tile, ++gt) {
-                    const int tb = gt & 1;
-                    if (gt >= 2) { tc::mbar_wait(&bars[6 + tb], (uint32_t)(((gt >> 1) - 1) & 1)); tc::fence_after_sync(); }
-                    const uint32_t d = tmem + (uint32_t)(tb * COUT);
-                    const uint64_t ad_tile = tc::smem_desc(a_base + (uint32_t)tile * 2048u, C::PLANE, 128);
+        // The whole warp walks the loop (warp-uniform control flow); one elected lane issues.
+        const bool leader = tc::elect_one();
+        const uint32_t idesc = tc::instr_desc_bf16(128, COUT, 0, 0);
+        const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sB), COUT * 16, 128);
+        int gt = 0;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b = c & 1;
+            tc::mbar_wait(&bars[b], (uint32_t)((c >> 1) & 1));
+            tc::fence_after_sync();
+            const uint32_t a_base = tc::smem_u32(sA0 + b * C::A_BYTES);
+            const int nt = chunk_tiles(c);
+            for (int tile = 0; tile < nt; ++tile, ++gt) {
+                const int tb = gt & 1;
+                if (gt >= 2) { tc::mbar_wait(&bars[6 + tb], (uint32_t)(((gt >> 1) - 1) & 1)); tc::fence_after_sync(); }
+                const uint32_t d = tmem + (uint32_t)(tb * COUT);
+                const uint64_t ad_tile = tc::smem_desc(a_base + (uint32_t)C::tile_start(tile) * 16u, C::PLANE, 128);
+                if (leader) {
 #pragma unroll
                     for (int tap = 0; tap < 25; ++tap) {
 #pragma unroll
@@ -218,8 +245,10 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
                     }
                     tc::mma_commit(&bars[4 + tb]);
                 }
-                tc::mma_commit(&bars[2 + b]);              // activation buffer b is free once these MMAs finish
+                __syncwarp();
             }
+            if (leader) tc::mma_commit(&bars[2 + b]);      // activation buffer b is free once these MMAs finish
+            __syncwarp();
         }
     } else {
         // ------------------------------ epilogue (warps 0-3) ------------------------------
@@ -238,7 +267,7 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
                 tc::tmem_ld_wait();
                 tc::fence_before_sync();
                 asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[6 + tb])) : "memory");
-                const int o = tile * 128 + t;               // origin handled by this thread (TMEM lane t)
+                const int o = C::tile_start(tile) + t;      // origin handled by this thread (TMEM lane t)
                 const int s = o / C::NPS, loc = o - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
                 if (s < ns && oy < H && ox < H) {
                     float *dst = out + (int64_t)(slot0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
@@ -302,12 +331,12 @@ int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 }
 int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 64, 7, 4, true>(ws.a2, ws.c3, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 64, 7, 3, true>(ws.a2, ws.c3, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                               TCO_W3U, OFF_B3, st);
 }
 int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<64, 32, 7, 2, false>(ws.dc3, ws.da2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<64, 32, 7, 3, false>(ws.dc3, ws.da2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                TCO_W3UD, 0, st);
 }
 int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
@@ -333,14 +362,15 @@ int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 template <int COUT, int H, int SB, bool PAIR = false>
 struct WgradTcCfg {
     static constexpr int CIN = 32;
-    static constexpr int PP = H + 4;
-    static constexpr int NPS = PP * PP;
+    using G = PlaneGeom<H>;
+    static constexpr int PP = G::PP, NPS = G::NPS;
     // dY is zero at every origin past the last valid one of the chunk's last sample, so the reduction
-    // stops there (H=15, SB=1: 281 of the 361 padded positions -> 18 K steps instead of 23)
-    static constexpr int NVALID = (SB - 1) * NPS + (H - 1) * PP + H;
+    // stops there (H = 15, SB = 1: 253 origins -> 16 K steps)
+    static constexpr int NVALID = (SB - 1) * NPS + G::NORIG;
     static constexpr int KPIX = ((NVALID + 1 + 15) / 16) * 16;     // reduction length per chunk (+1: shifted copy)
-    static constexpr int TAIL = ((4 * PP + 4 + 7) / 8) * 8;
-    static constexpr int NPD = KPIX, NPI = KPIX + TAIL;
+    static constexpr int TAIL = ((G::TAIL + 7) / 8) * 8;
+    static constexpr int FULL = (((SB - 1) * NPS + G::EXTENT + 7) / 8) * 8;
+    static constexpr int NPD = KPIX, NPI = (KPIX + TAIL > FULL) ? KPIX + TAIL : FULL;
     static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
     static constexpr int MROWS = PAIR ? 2 * COUT : 64;            // accumulator rows of one MMA
     static constexpr int DPLANES = MROWS / 8;                      // 8-channel dY planes (PAIR: two shifted copies)
@@ -363,13 +393,13 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
 {
     using C = WgradTcCfg<COUT, H, SB, PAIR>;
     static_assert(!PAIR || (C::NPD > C::NVALID), "pair trick needs a spare plane entry");
-    static_assert(C::NPI >= SB * C::NPS, "input planes must hold every padded pixel of the chunk");
+    static_assert(C::NPI >= C::FULL && C::NPI >= C::KPIX + C::TAIL, "input planes must hold every padded pixel of the chunk");
     static_assert(PAIR || COUT == 64, "without the pair trick the operand must have 64 real rows");
     constexpr int NMMA = PAIR ? 15 : C::TAPS0;           // accumulator tiles (32 columns each) per CTA
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + 2 * C::BUF);   // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int g = PAIR ? blockIdx.x : (blockIdx.x >> 1), half = PAIR ? 0 : (blockIdx.x & 1);
     if (p.gcount[g] <= 0) return;
     const int tap0 = half ? C::TAPS0 : 0, ntap = PAIR ? 15 : (half ? 25 - C::TAPS0 : C::TAPS0);
@@ -418,8 +448,10 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             tc::fence_async_smem();
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
         }
-    } else if (lane == 0) {
+    } else {
         // ------------------------------ MMA issuer ------------------------------
+        // warp-uniform control flow, one elected lane issues (no ELECT/BRA.U.ANY waterfall per MMA)
+        const bool leader = tc::elect_one();
         const uint32_t idesc = tc::instr_desc_bf16(C::MROWS, 32, 1, 1);
         uint32_t acc = 0;
         uint32_t tshift[NMMA];                       // tap shift in 16-byte units (registers: loops are unrolled)
@@ -439,18 +471,21 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             const uint32_t d_base = tc::smem_u32(smem + b * C::BUF);
             const uint64_t ad0 = tc::smem_desc(d_base, 128, C::PLANE_D);
             const uint64_t bd0 = tc::smem_desc(d_base + C::DPLANES * C::PLANE_D, 128, C::PLANE_I);
+            if (leader) {
 #pragma unroll 1
-            for (int j = 0; j < C::KPIX / 16; ++j) {
-                const uint64_t ad = ad0 + (uint64_t)(j * 16);
-                const uint64_t bdj = bd0 + (uint64_t)(j * 16);
+                for (int j = 0; j < C::KPIX / 16; ++j) {
+                    const uint64_t ad = ad0 + (uint64_t)(j * 16);
+                    const uint64_t bdj = bd0 + (uint64_t)(j * 16);
 #pragma unroll
-                for (int ti = 0; ti < NMMA; ++ti)
-                    if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
-                acc = 1;
+                    for (int ti = 0; ti < NMMA; ++ti)
+                        if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
+                    acc = 1;
+                }
+                tc::mma_commit(&bars[2 + b]);          // buffer b may be refilled once these MMAs are done
             }
-            tc::mma_commit(&bars[2 + b]);          // buffer b may be refilled once these MMAs are done
+            __syncwarp();
         }
-        tc::mma_commit(&bars[4]);
+        if (leader) tc::mma_commit(&bars[4]);
     }
     __syncwarp();
     // ------------------------------ epilogue: TMEM -> gradient row ------------------------------

@@ -97,7 +97,7 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
     uint32_t *s16 = reinterpret_cast<uint32_t *>(ring);      // bf16 image rows; dead before the ring is first written
 
-    const int slot = blockIdx.x, t = threadIdx.x, warp = t >> 5;
+    const int slot = blockIdx.x, t = threadIdx.x, warp = tc::uniform_warp_idx();
     const int id = p.img_idx[slot];
     if (id < 0) return;
     const int g = slot / p.gs;
@@ -135,7 +135,10 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
                         bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
         tc::mma_commit(&bars[k & 1]);
     };
-    if (t == 0) { issue(0); issue(1); }
+    if (warp == 0) {                     // one elected lane of a converged warp issues (no per-MMA waterfall)
+        if (tc::elect_one()) { issue(0); issue(1); }
+        __syncwarp();
+    }
 
     uint8_t *idx_out = ws.idx1 ? ws.idx1 + (int64_t)slot * A1_SZ : nullptr;
     for (int k = 0; k < 8; ++k) {
@@ -153,7 +156,10 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
         tc::fence_before_sync();
         __syncthreads();
         tc::fence_after_sync();
-        if (t == 0 && k + 2 < 8) issue(k + 2);
+        if (warp == 0 && k + 2 < 8) {
+            if (tc::elect_one()) issue(k + 2);
+            __syncwarp();
+        }
         // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins).
         // lane = channel; warp = (pooled row 0/1, quarter of the 15 columns): a thread loads the 3 x 9
         // conv values its (up to) four adjacent windows share and scans each window in (dy, dx) order.
@@ -247,7 +253,7 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
     uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 3072 + 512);       // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
     uint32_t *s16 = reinterpret_cast<uint32_t *>(simg + 3072 + 512 + 128);
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int g = blockIdx.x, gs = p.gs;
     if (p.gcount[g] <= 0) return;
     {
@@ -333,7 +339,8 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
             tc::fence_async_smem();
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
         }
-    } else if (lane == 0) {
+    } else {
+        const bool leader = tc::elect_one();          // warp-uniform loop, one elected lane issues
         const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
         uint32_t acc = 0;
         for (int s = 0; s < gs; ++s) {
@@ -344,15 +351,19 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
             const uint64_t ad0 = tc::smem_desc(e_base, 128, 512);                       // M chunks = ky, 32 entries apart
             const uint64_t ad1 = tc::smem_desc(e_base + E_PLANE, 128, 512);
             const uint64_t bd0 = tc::smem_desc(e_base + 2 * E_PLANE, 128, DC_PLANE);
+            if (leader) {
 #pragma unroll 4
-            for (int j = 0; j < 64; ++j) {
-                tc::mma_f16(tmem, ad0 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
-                tc::mma_f16(tmem + 32, ad1 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
-                acc = 1;
+                for (int j = 0; j < 64; ++j) {
+                    tc::mma_f16(tmem, ad0 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
+                    tc::mma_f16(tmem + 32, ad1 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
+                    acc = 1;
+                }
+                tc::mma_commit(&bars[2 + b]);
             }
-            tc::mma_commit(&bars[2 + b]);
+            acc = 1;
+            __syncwarp();
         }
-        tc::mma_commit(&bars[4]);
+        if (leader) tc::mma_commit(&bars[4]);
     }
     __syncwarp();
     if (warp < 4) {

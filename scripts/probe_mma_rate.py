@@ -27,16 +27,23 @@ def main():
     cyc = torch.zeros(1, dtype=torch.int64, device=dev)
     lib = _lib.lib()
     rep = 400
-    for name, M, N, amn, bmn, la, sa, lb, sb in [
+    for name, M, N, amn, bmn, la, sa, lb, sb, *rest in [
             ("K-major  M128 N32 ", 128, 32, 0, 0, 4096, 128, 512, 128),
+            ("K-major  M128 N32 A start +16 B (shifted window)", 128, 32, 0, 0, 4096, 128, 512, 128, 16),
+            ("K-major  M128 N32 A start +64 B", 128, 32, 0, 0, 4096, 128, 512, 128, 64),
+            ("K-major  M128 N64 A start +16 B", 128, 64, 0, 0, 4096, 128, 1024, 128, 16),
+            ("K-major  M128 N128 A start +16 B", 128, 128, 0, 0, 4096, 128, 2048, 128, 16),
+            ("MN-major M64  N32 B start +16 B", 64, 32, 1, 1, 128, 4096, 128, 4096, 0, 16),
             ("K-major  M128 N64 ", 128, 64, 0, 0, 4096, 128, 1024, 128),
             ("K-major  M128 N128", 128, 128, 0, 0, 4096, 128, 2048, 128),
             ("K-major  M64  N32 ", 64, 32, 0, 0, 4096, 128, 512, 128),
             ("MN-major M64  N32 ", 64, 32, 1, 1, 128, 4096, 128, 4096),
             ("MN-major M64  N64 ", 64, 64, 1, 1, 128, 4096, 128, 4096),
             ("MN-major M128 N32 ", 128, 32, 1, 1, 128, 2048, 128, 4096)]:
-        ad = torch.tensor(np.array([desc(i * 256, la, sa) for i in range(8)], dtype=np.uint64).view(np.int64), device=dev)
-        bd = torch.tensor(np.array([desc(i * 256, lb, sb) for i in range(8)], dtype=np.uint64).view(np.int64), device=dev)
+        a_off = rest[0] if len(rest) > 0 else 0
+        b_off = rest[1] if len(rest) > 1 else 0
+        ad = torch.tensor(np.array([desc(i * 256 + a_off, la, sa) for i in range(8)], dtype=np.uint64).view(np.int64), device=dev)
+        bd = torch.tensor(np.array([desc(i * 256 + b_off, lb, sb) for i in range(8)], dtype=np.uint64).view(np.int64), device=dev)
         rc = lib.dls_tc_probe(img.data_ptr(), img.numel(), img.data_ptr(), img.numel(), ad.data_ptr(), bd.data_ptr(), 8,
                               idesc(M, N, amn, bmn), 32, out.data_ptr(), rep, cyc.data_ptr(),
                               torch.cuda.current_stream().cuda_stream)

@@ -228,6 +228,227 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 }
 
 // ------------------------------------------------------------------------------------------
+// conv1 + maxpool as NINE shifted convolutions (the forward kernel in use).
+//
+// A pooled pixel (py, px) is the maximum over conv pixels (2py + dy, 2px + dx), dy, dx in 0..2.  For a
+// fixed (dy, dx) those conv pixels form a stride-2 sub-grid; with the expanded image split into four
+// parity planes (row parity x column parity, 16 entries per half row) that sub-grid is again a plain
+// shifted window, so tile T(dy, dx) — M = 128 rows = 8 pooled rows x 16 pooled columns — is five MMAs
+// (one per ky).  TMEM lane m of every tile is the SAME pooled pixel: the 3x3 maximum and its arg-max
+// are nine register compares per channel, in (dy, dx) order like the scan of the reference's
+// max_pool2d, with no shared-memory ring, no cross-lane traffic and no barriers between tiles.
+// The price is 90 MMAs per image instead of 40 (conv pixels shared by windows are recomputed); the
+// tensor pipe has the room, the CUDA cores do not.
+//   warps 0-3 / 4-7: pooled rows 0-7 / 8-14, one TMEM lane quadrant each: drain, pool, GroupNorm, store
+//   warp 8         : MMA issuer; tiles flow through a ring of eight 32-column TMEM accumulators
+// ------------------------------------------------------------------------------------------
+constexpr int EP_PLANE = 20 * 16 * 16;        // parity plane: 18 half-rows of 16 entries (+2 rows junk lanes may read)
+constexpr int C1P_THREADS = 288;
+constexpr int C1P_SLOTS = 8;
+constexpr int C1P_SMEM = 8 * EP_PLANE + C1_W_BYTES + S16_BYTES + 3072 + 512 + 3 * 32 * 4 + 2 * 16 * 4 +
+                         2 * C1P_SLOTS * 8 + 64;
+
+// E entries into parity planes: plane ((pr&1)*2 + (ox&1))*2 + j, entry (pr>>1)*16 + (ox>>1).
+__device__ __forceinline__ void build_expanded_parity(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
+{
+    for (int i = t; i < 36 * 32 * 2; i += nthreads) {
+        const int oxh = i & 15, j = (i >> 4) & 1, cpar = (i >> 5) & 1, pr = i >> 6;
+        const int ox = 2 * oxh + cpar, y = pr - 2;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (y >= 0 && y < 32) {
+            const int off = ox * 3 + 8 * j;
+            const uint32_t *rw = s16 + y * (ROW16 / 2) + (off >> 1);
+            const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
+            if (off & 1) {
+                v.x = __funnelshift_r(w0, w1, 16); v.y = __funnelshift_r(w1, w2, 16);
+                v.z = __funnelshift_r(w2, w3, 16); v.w = __funnelshift_r(w3, w4, 16);
+            } else {
+                v.x = w0; v.y = w1; v.z = w2; v.w = w3;
+            }
+            if (j) v.w &= 0x0000FFFFu;
+        }
+        *reinterpret_cast<uint4 *>(sE + ((((pr & 1) * 2 + cpar) * 2 + j) * EP_PLANE) + ((pr >> 1) * 16 + oxh) * 16) = v;
+    }
+}
+
+__device__ __forceinline__ void pool_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__global__ void __launch_bounds__(C1P_THREADS, 2)
+conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *sE = smem;
+    uint8_t *sW = sE + 8 * EP_PLANE;
+    uint32_t *s16 = reinterpret_cast<uint32_t *>(sW + C1_W_BYTES);
+    uint8_t *simg = reinterpret_cast<uint8_t *>(s16) + S16_BYTES;
+    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
+    float *sbias = reinterpret_cast<float *>(simg + 3072 + 512);
+    float *sgam = sbias + 32, *sbet = sgam + 32;
+    float *red1 = sbet + 32, *red2 = red1 + 16;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(red2 + 16);            // full[SLOTS], empty[SLOTS]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * C1P_SLOTS);
+
+    const int slot = blockIdx.x, t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
+    const int id = p.img_idx[slot];
+    if (id < 0) return;
+    const int g = slot / p.gs;
+    int m;
+    const float *row = model_row(p, g, m);
+
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
+        for (int i = t; i < IMG_BYTES / 16; i += C1P_THREADS) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
+        const uint4 *wsrc = reinterpret_cast<const uint4 *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
+                                                             (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
+        for (int i = t; i < C1_W_BYTES / 16; i += C1P_THREADS) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
+        for (int i = t; i < 256; i += C1P_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
+        if (t < 32) { sbias[t] = row[OFF_B1 + t]; sgam[t] = row[OFF_G1W + t]; sbet[t] = row[OFF_G1B + t]; }
+    }
+    if (t == 0) {
+        for (int i = 0; i < C1P_SLOTS; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&bars[C1P_SLOTS + i], 128); }
+        tc::mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 32 * C1P_SLOTS);
+    __syncthreads();
+    convert_rows(simg, lut, s16, t, C1P_THREADS);
+    __syncthreads();
+    build_expanded_parity(s16, sE, t, C1P_THREADS);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 8) {
+        // ------------------------------ MMA issuer ------------------------------
+        const bool leader = tc::elect_one();
+        const uint32_t idesc = tc::instr_desc_bf16(128, 32, 0, 0);
+        const uint64_t ad0 = tc::smem_desc(tc::smem_u32(sE), EP_PLANE, 128);
+        const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sW), 32 * 16, 128);
+#pragma unroll
+        for (int seq = 0; seq < 18; ++seq) {
+            const int mt = seq & 1, tt = seq >> 1, dy = tt / 3, dx = tt % 3, sl = seq % C1P_SLOTS;
+            if (seq >= C1P_SLOTS) {
+                tc::mbar_wait(&bars[C1P_SLOTS + sl], (uint32_t)(((seq / C1P_SLOTS) - 1) & 1));
+                tc::fence_after_sync();
+            }
+            if (leader) {
+#pragma unroll
+                for (int ky = 0; ky < 5; ++ky) {
+                    const int sy = dy + ky;
+                    const int plane = ((sy & 1) * 2 + (dx & 1)) * 2;
+                    const int entry = (8 * mt + (sy >> 1)) * 16 + (dx >> 1);
+                    tc::mma_f16(tmem + (uint32_t)(sl * 32), ad0 + (uint64_t)((plane * EP_PLANE + entry * 16) >> 4),
+                                bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
+                }
+                tc::mma_commit(&bars[sl]);
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ------------------------------ pool / normalise (warps 0-7) ------------------------------
+    const int mt = warp >> 2, q = warp & 3;
+    const int mrow = q * 32 + lane, py = 8 * mt + (mrow >> 4), px = mrow & 15;
+    const bool valid = py < 15 && px < 15;
+    // The bias is added after the maximum: rounding is monotone, so the maximum VALUE is the one of
+    // max(x + b); only an exact tie created by that rounding could pick a later window position.
+    float best[32];
+    uint32_t bi[8];                      // arg-max position (0..8) per channel, one byte each (idx1 layout)
+#pragma unroll
+    for (int w = 0; w < 8; ++w) bi[w] = 0u;
+#pragma unroll
+    for (int tt = 0; tt < 9; ++tt) {
+        const int seq = 2 * tt + mt, sl = seq % C1P_SLOTS;
+        tc::mbar_wait(&bars[sl], (uint32_t)((seq / C1P_SLOTS) & 1));
+        tc::fence_after_sync();
+        uint32_t r[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(sl * 32), r);
+        tc::tmem_ld_wait();
+        tc::fence_before_sync();
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[C1P_SLOTS + sl])) : "memory");
+        if (tt == 0) {
+#pragma unroll
+            for (int co = 0; co < 32; ++co) best[co] = __uint_as_float(r[co]);
+        } else {
+#pragma unroll
+            for (int co = 0; co < 32; ++co) {
+                const float x = __uint_as_float(r[co]);
+                if (x > best[co]) {                                   // strict >: the first maximum wins
+                    best[co] = x;
+                    // replace byte (co & 3) of the packed index word by tt
+                    bi[co >> 2] = __byte_perm(bi[co >> 2], (uint32_t)tt, 0x3210u ^ ((0x3210u >> (4 * (co & 3)) & 0xFu) << (4 * (co & 3))) ^ (0x4u << (4 * (co & 3))));
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int co = 0; co < 32; ++co) best[co] += sbias[co];
+
+    // GroupNorm(2, 32): two passes over the registers (mean, then centred sum of squares)
+    float s0 = 0.f, s1 = 0.f;
+    if (valid) {
+#pragma unroll
+        for (int co = 0; co < 16; ++co) { s0 += best[co]; s1 += best[16 + co]; }
+    }
+    s0 = warp_sum(s0); s1 = warp_sum(s1);
+    if (lane == 0) { red1[warp * 2] = s0; red1[warp * 2 + 1] = s1; }
+    pool_bar();
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { sum0 += red1[w * 2]; sum1 += red1[w * 2 + 1]; }
+    const float inv_n = 1.f / 3600.f;
+    const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
+    float q0 = 0.f, q1 = 0.f;
+    if (valid) {
+#pragma unroll
+        for (int co = 0; co < 16; ++co) {
+            const float d0 = best[co] - mean0, d1 = best[16 + co] - mean1;
+            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1);
+        }
+    }
+    q0 = warp_sum(q0); q1 = warp_sum(q1);
+    if (lane == 0) { red2[warp * 2] = q0; red2[warp * 2 + 1] = q1; }
+    pool_bar();
+    float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { v0 += red2[w * 2]; v1 += red2[w * 2 + 1]; }
+    const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
+
+    if (valid) {
+        const int pp = py * 15 + px;
+        float4 *a1 = reinterpret_cast<float4 *>(ws.a1 + (int64_t)slot * A1_SZ + pp * 32);
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int co = c4 * 4 + e;
+                const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
+                const float v = (best[co] - mean) * rstd * sgam[co] + sbet[co];
+                o[e] = v > 0.f ? v : 0.f;
+            }
+            a1[c4] = make_float4(o[0], o[1], o[2], o[3]);
+        }
+        if (save_bwd) {
+            float4 *p1 = reinterpret_cast<float4 *>(ws.p1 + (int64_t)slot * A1_SZ + pp * 32);
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4)
+                p1[c4] = make_float4(best[c4 * 4], best[c4 * 4 + 1], best[c4 * 4 + 2], best[c4 * 4 + 3]);
+            uint4 *ix = reinterpret_cast<uint4 *>(ws.idx1 + (int64_t)slot * A1_SZ + pp * 32);
+            ix[0] = make_uint4(bi[0], bi[1], bi[2], bi[3]);
+            ix[1] = make_uint4(bi[4], bi[5], bi[6], bi[7]);
+        }
+    }
+    if (save_bwd && t == 0) {
+        float *st = ws.st1 + (int64_t)slot * 4;
+        st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
+    }
+    if (warp == 0) tc::tmem_dealloc(tmem, 32 * C1P_SLOTS);      // every consumer passed two barriers after its last TMEM read
+}
+
+// ------------------------------------------------------------------------------------------
 // conv1 weight gradient on tensor cores.
 //   dW1[co][c][ky][kx] = sum over samples and conv-output positions o of dc1[o][co] * P[o + (ky,kx)][c]
 // where dc1 is the gradient w.r.t. the conv1 output: the pooled gradient dp1 routed to the arg-max
@@ -439,11 +660,11 @@ int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
 {
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1F_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv1_pool_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1P_SMEM);
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    conv1_tc_kernel<<<p.n_groups * p.gs, C1F_THREADS, C1F_SMEM, st>>>(p, ws, save ? 1 : 0);
+    conv1_pool_tc_kernel<<<p.n_groups * p.gs, C1P_THREADS, C1P_SMEM, st>>>(p, ws, save ? 1 : 0);
     DLS_LAUNCH_CHECK();
     return 0;
 }

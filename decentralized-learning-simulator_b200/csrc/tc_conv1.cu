@@ -243,10 +243,13 @@ conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
 //   warp 8         : MMA issuer; tiles flow through a ring of eight 32-column TMEM accumulators
 // ------------------------------------------------------------------------------------------
 constexpr int EP_PLANE = 20 * 16 * 16;        // parity plane: 18 half-rows of 16 entries (+2 rows junk lanes may read)
-constexpr int C1P_THREADS = 288;
-constexpr int C1P_SLOTS = 8;
-constexpr int C1P_SMEM = 8 * EP_PLANE + C1_W_BYTES + S16_BYTES + 3072 + 512 + 3 * 32 * 4 + 2 * 16 * 4 +
-                         2 * C1P_SLOTS * 8 + 64;
+constexpr int C1P_POOL = 256, C1P_PRODUCERS = 96;
+constexpr int C1P_THREADS = C1P_POOL + 32 + C1P_PRODUCERS;     // warps 0-7 pool, warp 8 issuer, warps 9-11 producers
+constexpr int C1P_SLOTS = 8;                   // TMEM accumulator ring (32 columns each)
+constexpr int C1P_STAGE = 8 * EP_PLANE + C1_W_BYTES;           // one staged image: parity planes + the node's W1
+constexpr int C1P_CAP = 256;                  // sample slots per CTA (descriptor table in shared memory)
+constexpr int C1P_SMEM = 2 * C1P_STAGE + S16_BYTES + 2 * 3072 + 512 + 4 * 96 * 4 + 4 * 16 * 4 +
+                         (4 + 2 * C1P_SLOTS) * 8 + 64 + 4 * C1P_CAP * 4;
 
 // E entries into parity planes: plane ((pr&1)*2 + (ox&1))*2 + j, entry (pr>>1)*16 + (ox>>1).
 __device__ __forceinline__ void build_expanded_parity(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
@@ -272,180 +275,250 @@ __device__ __forceinline__ void build_expanded_parity(const uint32_t *s16, uint8
 }
 
 __device__ __forceinline__ void pool_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void c1p_producer_bar() { asm volatile("bar.sync 2, 96;" ::: "memory"); }
 
+// Persistent: a CTA owns a contiguous range of sample slots (two CTAs per SM, ranges differ by at most
+// one sample, so the SMs are balanced at sample granularity) and pipelines them: the producers expand
+// image i+1 into the other stage while the issuer and the pool warps work on image i.
 __global__ void __launch_bounds__(C1P_THREADS, 2)
 conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *sE = smem;
-    uint8_t *sW = sE + 8 * EP_PLANE;
-    uint32_t *s16 = reinterpret_cast<uint32_t *>(sW + C1_W_BYTES);
+    uint8_t *stage0 = smem;                                                // [2][planes | W1]
+    uint32_t *s16 = reinterpret_cast<uint32_t *>(smem + 2 * C1P_STAGE);    // producers' scratch
     uint8_t *simg = reinterpret_cast<uint8_t *>(s16) + S16_BYTES;
-    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
-    float *sbias = reinterpret_cast<float *>(simg + 3072 + 512);
-    float *sgam = sbias + 32, *sbet = sgam + 32;
-    float *red1 = sbet + 32, *red2 = red1 + 16;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(red2 + 16);            // full[SLOTS], empty[SLOTS]
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * C1P_SLOTS);
+    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 2 * 3072);          // simg: two raw images
+    float *params = reinterpret_cast<float *>(simg + 2 * 3072 + 512);      // [4][bias 32 | gamma 32 | beta 32]
+    float *red = params + 4 * 96;                                          // [2 parities][2 passes][16]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(red + 4 * 16);           // full[2] empty[2] tfull[S] tempty[S]
+    uint64_t *tfull = bars + 4, *tempty = tfull + C1P_SLOTS;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + C1P_SLOTS);
+    int32_t *tab_slot = reinterpret_cast<int32_t *>(tmem_slot + 16);       // active samples of this CTA, compacted
+    int32_t *tab_id = tab_slot + C1P_CAP, *tab_m = tab_id + C1P_CAP, *tab_row = tab_m + C1P_CAP;
+    __shared__ int n_active_s;
 
-    const int slot = blockIdx.x, t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
-    const int id = p.img_idx[slot];
-    if (id < 0) return;
-    const int g = slot / p.gs;
-    int m;
-    const float *row = model_row(p, g, m);
-
-    {
-        const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
-        for (int i = t; i < IMG_BYTES / 16; i += C1P_THREADS) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
-        const uint4 *wsrc = reinterpret_cast<const uint4 *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
-                                                             (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
-        for (int i = t; i < C1_W_BYTES / 16; i += C1P_THREADS) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
-        for (int i = t; i < 256; i += C1P_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
-        if (t < 32) { sbias[t] = row[OFF_B1 + t]; sgam[t] = row[OFF_G1W + t]; sbet[t] = row[OFF_G1B + t]; }
+    const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
+    const int n_slots = p.n_groups * p.gs;
+    const int s_begin = (int)(((int64_t)blockIdx.x * n_slots) / gridDim.x);
+    const int s_end = (int)(((int64_t)(blockIdx.x + 1) * n_slots) / gridDim.x);
+    // descriptor table: no dependent global loads inside the pipelined loops
+    if (warp == 0) {
+        int n = 0;
+        for (int base = s_begin; base < s_end; base += 32) {
+            const int sl = base + lane;
+            const int id = sl < s_end ? p.img_idx[sl] : -1;
+            const unsigned mask = __ballot_sync(0xffffffffu, id >= 0);
+            if (id >= 0) {
+                const int pos = n + __popc(mask & ((1u << lane) - 1u));
+                const int g = sl / p.gs;
+                const int mm = p.gmodel ? p.gmodel[g] : g;
+                tab_slot[pos] = sl; tab_id[pos] = id; tab_m[pos] = mm; tab_row[pos] = p.mrow[mm];
+            }
+            n += __popc(mask);
+        }
+        if (lane == 0) n_active_s = n;
     }
+
+    for (int i = t; i < 256; i += C1P_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
     if (t == 0) {
-        for (int i = 0; i < C1P_SLOTS; ++i) { tc::mbar_init(&bars[i], 1); tc::mbar_init(&bars[C1P_SLOTS + i], 128); }
+        tc::mbar_init(&bars[0], C1P_PRODUCERS); tc::mbar_init(&bars[1], C1P_PRODUCERS);
+        tc::mbar_init(&bars[2], 1); tc::mbar_init(&bars[3], 1);
+        for (int i = 0; i < C1P_SLOTS; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], 128); }
         tc::mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, 32 * C1P_SLOTS);
-    __syncthreads();
-    convert_rows(simg, lut, s16, t, C1P_THREADS);
-    __syncthreads();
-    build_expanded_parity(s16, sE, t, C1P_THREADS);
-    tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *tmem_slot;
+    const int n_active = n_active_s;
 
-    if (warp == 8) {
+    if (warp >= 9) {
+        // ------------------------------ producers ------------------------------
+        // All global traffic is asynchronous (cp.async): the raw bytes of image it+1 are in flight while
+        // image it is expanded, W1 / bias / gamma / beta of image it land during its expansion.
+        const int pt = t - (C1P_POOL + 32);
+        auto fetch_image = [&](int k, int buf) {
+            if (k < n_active) {
+                const uint8_t *src = p.images + (int64_t)tab_id[k] * IMG_BYTES;
+                uint8_t *dst = simg + buf * 3072;
+                tc::cp_async16(dst + pt * 16, src + pt * 16);
+                tc::cp_async16(dst + (pt + C1P_PRODUCERS) * 16, src + (pt + C1P_PRODUCERS) * 16);
+            }
+            tc::cp_async_commit();
+        };
+        fetch_image(0, 0);
+        for (int it = 0; it < n_active; ++it) {
+            const int b = it & 1;
+            const int m = tab_m[it];
+            const float *row = p.X + (int64_t)tab_row[it] * p.ldx;
+            uint8_t *sE = stage0 + b * C1P_STAGE;
+            if (it >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((it >> 1) - 1) & 1));      // MMAs of image it-2 done
+            {
+                const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
+                                                                         (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
+                uint8_t *wdst = sE + 8 * EP_PLANE;
+                for (int i = pt; i < C1_W_BYTES / 16; i += C1P_PRODUCERS) tc::cp_async16(wdst + i * 16, wsrc + i * 16);
+                if (pt < 24) {                                           // bias | gamma | beta: 3 x 128 bytes
+                    const int off = pt < 8 ? OFF_B1 : (pt < 16 ? OFF_G1W : OFF_G1B);
+                    tc::cp_async16(params + (it & 3) * 96 + pt * 4, row + off + (pt & 7) * 4);
+                }
+                tc::cp_async_commit();
+            }
+            fetch_image(it + 1, (it + 1) & 1);
+            tc::cp_async_wait<2>();                                      // image it has landed
+            c1p_producer_bar();
+            convert_rows(simg + b * 3072, lut, s16, pt, C1P_PRODUCERS);
+            c1p_producer_bar();
+            build_expanded_parity(s16, sE, pt, C1P_PRODUCERS);
+            tc::cp_async_wait<1>();                                      // W1 and the parameters of image it
+            tc::fence_async_smem();
+            tc::mbar_arrive(&bars[b]);
+        }
+        tc::cp_async_wait<0>();
+    } else if (warp == 8) {
         // ------------------------------ MMA issuer ------------------------------
         const bool leader = tc::elect_one();
         const uint32_t idesc = tc::instr_desc_bf16(128, 32, 0, 0);
-        const uint64_t ad0 = tc::smem_desc(tc::smem_u32(sE), EP_PLANE, 128);
-        const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sW), 32 * 16, 128);
+        for (int it = 0; it < n_active; ++it) {
+            const int b = it & 1;
+            tc::mbar_wait(&bars[b], (uint32_t)((it >> 1) & 1));
+            tc::fence_after_sync();
+            const uint32_t e_base = tc::smem_u32(stage0 + b * C1P_STAGE);
+            const uint64_t ad0 = tc::smem_desc(e_base, EP_PLANE, 128);
+            const uint64_t bd0 = tc::smem_desc(e_base + 8 * EP_PLANE, 32 * 16, 128);
 #pragma unroll
-        for (int seq = 0; seq < 18; ++seq) {
-            const int mt = seq & 1, tt = seq >> 1, dy = tt / 3, dx = tt % 3, sl = seq % C1P_SLOTS;
-            if (seq >= C1P_SLOTS) {
-                tc::mbar_wait(&bars[C1P_SLOTS + sl], (uint32_t)(((seq / C1P_SLOTS) - 1) & 1));
-                tc::fence_after_sync();
-            }
-            if (leader) {
-#pragma unroll
-                for (int ky = 0; ky < 5; ++ky) {
-                    const int sy = dy + ky;
-                    const int plane = ((sy & 1) * 2 + (dx & 1)) * 2;
-                    const int entry = (8 * mt + (sy >> 1)) * 16 + (dx >> 1);
-                    tc::mma_f16(tmem + (uint32_t)(sl * 32), ad0 + (uint64_t)((plane * EP_PLANE + entry * 16) >> 4),
-                                bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
+            for (int seq = 0; seq < 18; ++seq) {
+                const int mt = seq & 1, tt = seq >> 1, dy = tt / 3, dx = tt % 3;
+                const int gseq = it * 18 + seq, sl = gseq & (C1P_SLOTS - 1);
+                if (gseq >= C1P_SLOTS) {
+                    tc::mbar_wait(&tempty[sl], (uint32_t)(((gseq / C1P_SLOTS) - 1) & 1));
+                    tc::fence_after_sync();
                 }
-                tc::mma_commit(&bars[sl]);
+                if (leader) {
+#pragma unroll
+                    for (int ky = 0; ky < 5; ++ky) {
+                        const int sy = dy + ky;
+                        const int plane = ((sy & 1) * 2 + (dx & 1)) * 2;
+                        const int entry = (8 * mt + (sy >> 1)) * 16 + (dx >> 1);
+                        tc::mma_f16(tmem + (uint32_t)(sl * 32), ad0 + (uint64_t)((plane * EP_PLANE + entry * 16) >> 4),
+                                    bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
+                    }
+                    tc::mma_commit(&tfull[sl]);
+                }
+                __syncwarp();
             }
+            if (leader) tc::mma_commit(&bars[2 + b]);          // the stage is free once these MMAs are done
             __syncwarp();
         }
-        return;
-    }
-
-    // ------------------------------ pool / normalise (warps 0-7) ------------------------------
-    const int mt = warp >> 2, q = warp & 3;
-    const int mrow = q * 32 + lane, py = 8 * mt + (mrow >> 4), px = mrow & 15;
-    const bool valid = py < 15 && px < 15;
-    // The bias is added after the maximum: rounding is monotone, so the maximum VALUE is the one of
-    // max(x + b); only an exact tie created by that rounding could pick a later window position.
-    float best[32];
-    uint32_t bi[8];                      // arg-max position (0..8) per channel, one byte each (idx1 layout)
+    } else {
+        // ------------------------------ pool / normalise (warps 0-7) ------------------------------
+        const int mt = warp >> 2, q = warp & 3;
+        const int mrow = q * 32 + lane, py = 8 * mt + (mrow >> 4), px = mrow & 15;
+        const bool valid = py < 15 && px < 15;
+        const int pp = py * 15 + px;
+        for (int it = 0; it < n_active; ++it) {
+            const int slot = tab_slot[it];
+            const float *prm = params + (it & 3) * 96;
+            float *red1 = red + (it & 1) * 32, *red2 = red1 + 16;
+            tc::mbar_wait(&bars[it & 1], (uint32_t)((it >> 1) & 1));      // acquire the producers' parameter writes
+            // The bias is added after the maximum: rounding is monotone, so the maximum VALUE is the one of
+            // max(x + b); only an exact tie created by that rounding could pick a later window position.
+            float best[32];
+            uint32_t bi[8];              // arg-max position (0..8) per channel, one byte each (idx1 layout)
 #pragma unroll
-    for (int w = 0; w < 8; ++w) bi[w] = 0u;
+            for (int w = 0; w < 8; ++w) bi[w] = 0u;
 #pragma unroll
-    for (int tt = 0; tt < 9; ++tt) {
-        const int seq = 2 * tt + mt, sl = seq % C1P_SLOTS;
-        tc::mbar_wait(&bars[sl], (uint32_t)((seq / C1P_SLOTS) & 1));
-        tc::fence_after_sync();
-        uint32_t r[32];
-        tc::tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(sl * 32), r);
-        tc::tmem_ld_wait();
-        tc::fence_before_sync();
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[C1P_SLOTS + sl])) : "memory");
-        if (tt == 0) {
+            for (int tt = 0; tt < 9; ++tt) {
+                const int gseq = it * 18 + 2 * tt + mt, sl = gseq & (C1P_SLOTS - 1);
+                tc::mbar_wait(&tfull[sl], (uint32_t)((gseq / C1P_SLOTS) & 1));
+                tc::fence_after_sync();
 #pragma unroll
-            for (int co = 0; co < 32; ++co) best[co] = __uint_as_float(r[co]);
-        } else {
+                for (int hf = 0; hf < 2; ++hf) {
+                    uint32_t r[16];
+                    tc::tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(sl * 32 + hf * 16), r);
+                    tc::tmem_ld_wait();
+                    if (hf == 1) { tc::fence_before_sync(); tc::mbar_arrive(&tempty[sl]); }
 #pragma unroll
-            for (int co = 0; co < 32; ++co) {
-                const float x = __uint_as_float(r[co]);
-                if (x > best[co]) {                                   // strict >: the first maximum wins
-                    best[co] = x;
-                    // replace byte (co & 3) of the packed index word by tt
-                    bi[co >> 2] = __byte_perm(bi[co >> 2], (uint32_t)tt, 0x3210u ^ ((0x3210u >> (4 * (co & 3)) & 0xFu) << (4 * (co & 3))) ^ (0x4u << (4 * (co & 3))));
+                    for (int c = 0; c < 16; ++c) {
+                        const int co = hf * 16 + c;
+                        const float x = __uint_as_float(r[c]);
+                        if (tt == 0) {
+                            best[co] = x;
+                        } else if (x > best[co]) {                    // strict >: the first maximum wins
+                            best[co] = x;
+                            bi[co >> 2] = __byte_perm(bi[co >> 2], (uint32_t)tt,
+                                                      (0x3210u & ~(0xFu << (4 * (co & 3)))) | (0x4u << (4 * (co & 3))));
+                        }
+                    }
                 }
             }
-        }
-    }
 #pragma unroll
-    for (int co = 0; co < 32; ++co) best[co] += sbias[co];
+            for (int co = 0; co < 32; ++co) best[co] += prm[co];
 
-    // GroupNorm(2, 32): two passes over the registers (mean, then centred sum of squares)
-    float s0 = 0.f, s1 = 0.f;
-    if (valid) {
+            // GroupNorm(2, 32): two passes over the registers (mean, then centred sum of squares)
+            float s0 = 0.f, s1 = 0.f;
+            if (valid) {
 #pragma unroll
-        for (int co = 0; co < 16; ++co) { s0 += best[co]; s1 += best[16 + co]; }
-    }
-    s0 = warp_sum(s0); s1 = warp_sum(s1);
-    if (lane == 0) { red1[warp * 2] = s0; red1[warp * 2 + 1] = s1; }
-    pool_bar();
-    float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) { sum0 += red1[w * 2]; sum1 += red1[w * 2 + 1]; }
-    const float inv_n = 1.f / 3600.f;
-    const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
-    float q0 = 0.f, q1 = 0.f;
-    if (valid) {
-#pragma unroll
-        for (int co = 0; co < 16; ++co) {
-            const float d0 = best[co] - mean0, d1 = best[16 + co] - mean1;
-            q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1);
-        }
-    }
-    q0 = warp_sum(q0); q1 = warp_sum(q1);
-    if (lane == 0) { red2[warp * 2] = q0; red2[warp * 2 + 1] = q1; }
-    pool_bar();
-    float v0 = 0.f, v1 = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) { v0 += red2[w * 2]; v1 += red2[w * 2 + 1]; }
-    const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
-
-    if (valid) {
-        const int pp = py * 15 + px;
-        float4 *a1 = reinterpret_cast<float4 *>(ws.a1 + (int64_t)slot * A1_SZ + pp * 32);
-#pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-            float o[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int co = c4 * 4 + e;
-                const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
-                const float v = (best[co] - mean) * rstd * sgam[co] + sbet[co];
-                o[e] = v > 0.f ? v : 0.f;
+                for (int co = 0; co < 16; ++co) { s0 += best[co]; s1 += best[16 + co]; }
             }
-            a1[c4] = make_float4(o[0], o[1], o[2], o[3]);
-        }
-        if (save_bwd) {
-            float4 *p1 = reinterpret_cast<float4 *>(ws.p1 + (int64_t)slot * A1_SZ + pp * 32);
+            s0 = warp_sum(s0); s1 = warp_sum(s1);
+            if (lane == 0) { red1[warp * 2] = s0; red1[warp * 2 + 1] = s1; }
+            pool_bar();
+            float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-            for (int c4 = 0; c4 < 8; ++c4)
-                p1[c4] = make_float4(best[c4 * 4], best[c4 * 4 + 1], best[c4 * 4 + 2], best[c4 * 4 + 3]);
-            uint4 *ix = reinterpret_cast<uint4 *>(ws.idx1 + (int64_t)slot * A1_SZ + pp * 32);
-            ix[0] = make_uint4(bi[0], bi[1], bi[2], bi[3]);
-            ix[1] = make_uint4(bi[4], bi[5], bi[6], bi[7]);
+            for (int w = 0; w < 8; ++w) { sum0 += red1[w * 2]; sum1 += red1[w * 2 + 1]; }
+            const float inv_n = 1.f / 3600.f;
+            const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
+            float q0 = 0.f, q1 = 0.f;
+            if (valid) {
+#pragma unroll
+                for (int co = 0; co < 16; ++co) {
+                    const float d0 = best[co] - mean0, d1 = best[16 + co] - mean1;
+                    q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1);
+                }
+            }
+            q0 = warp_sum(q0); q1 = warp_sum(q1);
+            if (lane == 0) { red2[warp * 2] = q0; red2[warp * 2 + 1] = q1; }
+            pool_bar();
+            float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) { v0 += red2[w * 2]; v1 += red2[w * 2 + 1]; }
+            const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
+
+            if (valid) {
+                if (save_bwd) {
+                    float4 *p1 = reinterpret_cast<float4 *>(ws.p1 + (int64_t)slot * A1_SZ + pp * 32);
+#pragma unroll
+                    for (int c4 = 0; c4 < 8; ++c4)
+                        p1[c4] = make_float4(best[c4 * 4], best[c4 * 4 + 1], best[c4 * 4 + 2], best[c4 * 4 + 3]);
+                    uint4 *ix = reinterpret_cast<uint4 *>(ws.idx1 + (int64_t)slot * A1_SZ + pp * 32);
+                    ix[0] = make_uint4(bi[0], bi[1], bi[2], bi[3]);
+                    ix[1] = make_uint4(bi[4], bi[5], bi[6], bi[7]);
+                }
+                float4 *a1 = reinterpret_cast<float4 *>(ws.a1 + (int64_t)slot * A1_SZ + pp * 32);
+#pragma unroll
+                for (int c4 = 0; c4 < 8; ++c4) {
+                    float o[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int co = c4 * 4 + e;
+                        const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
+                        const float v = (best[co] - mean) * rstd * prm[32 + co] + prm[64 + co];
+                        o[e] = v > 0.f ? v : 0.f;
+                    }
+                    a1[c4] = make_float4(o[0], o[1], o[2], o[3]);
+                }
+            }
+            if (save_bwd && t == 0) {
+                float *st = ws.st1 + (int64_t)slot * 4;
+                st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
+            }
         }
     }
-    if (save_bwd && t == 0) {
-        float *st = ws.st1 + (int64_t)slot * 4;
-        st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
-    }
-    if (warp == 0) tc::tmem_dealloc(tmem, 32 * C1P_SLOTS);      // every consumer passed two barriers after its last TMEM read
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 32 * C1P_SLOTS);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -664,7 +737,10 @@ int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    conv1_pool_tc_kernel<<<p.n_groups * p.gs, C1P_THREADS, C1P_SMEM, st>>>(p, ws, save ? 1 : 0);
+    const int n_slots = p.n_groups * p.gs;
+    int grid = n_slots < 2 * 148 ? n_slots : 2 * 148;              // two persistent CTAs per SM
+    if ((n_slots + grid - 1) / grid > C1P_CAP) grid = (n_slots + C1P_CAP - 1) / C1P_CAP;
+    conv1_pool_tc_kernel<<<grid, C1P_THREADS, C1P_SMEM, st>>>(p, ws, save ? 1 : 0);
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -274,6 +274,54 @@ __device__ __forceinline__ void build_expanded_parity(const uint32_t *s16, uint8
     }
 }
 
+// Producer-side versions for exactly C1P_PRODUCERS = 96 threads with loop-invariant index math.
+// The pad words of the bf16 rows are zeroed once per CTA (s16 is producer-private scratch).
+__device__ __forceinline__ void c1p_zero_row_pads(uint32_t *s16, int pt)
+{
+    for (int i = pt; i < 32 * 10; i += C1P_PRODUCERS) {
+        const int row = i / 10, k = i - row * 10;
+        s16[row * (ROW16 / 2) + (k < 3 ? k : 48 + k)] = 0u;              // words 0-2 and 51-57
+    }
+}
+// thread -> data word w (two bytes -> two bf16) of rows r0, r0+2, ...: sixteen independent chains
+__device__ __forceinline__ void c1p_convert_rows(const uint8_t *simg, const __nv_bfloat16 *lut, uint32_t *s16, int pt)
+{
+    const int w = pt % 48, r0 = pt / 48;
+    const unsigned short *lut16 = reinterpret_cast<const unsigned short *>(lut);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int row = r0 + 2 * k;
+        const uint32_t two = *reinterpret_cast<const unsigned short *>(simg + row * 96 + 2 * w);
+        s16[row * (ROW16 / 2) + 3 + w] = (uint32_t)lut16[two & 0xFFu] | ((uint32_t)lut16[two >> 8] << 16);
+    }
+}
+// thread -> (entry column ox, half j) and a third of the 36 padded rows; 2 passes x 12 rows
+__device__ __forceinline__ void c1p_build_expanded(const uint32_t *s16, uint8_t *sE, int pt)
+{
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+        const int sl = pt + C1P_PRODUCERS * pass;
+        const int combo = sl & 63, third = sl >> 6;
+        const int oxh = combo & 15, j = (combo >> 4) & 1, cpar = combo >> 5;
+        const int off = (2 * oxh + cpar) * 3 + 8 * j;
+        const uint32_t sh = (off & 1) ? 16u : 0u, mask_w = j ? 0x0000FFFFu : 0xFFFFFFFFu;
+        const uint32_t *col = s16 + (off >> 1);
+        uint8_t *dcol = sE + (cpar * 2 + j) * EP_PLANE + oxh * 16;
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            const int pr = third * 12 + k, y = pr - 2;                    // 12 is even: pr & 1 == k & 1
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (y >= 0 && y < 32) {
+                const uint32_t *rw = col + y * (ROW16 / 2);
+                const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
+                v.x = __funnelshift_r(w0, w1, sh); v.y = __funnelshift_r(w1, w2, sh);
+                v.z = __funnelshift_r(w2, w3, sh); v.w = __funnelshift_r(w3, w4, sh) & mask_w;
+            }
+            *reinterpret_cast<uint4 *>(dcol + (k & 1) * 4 * EP_PLANE + (pr >> 1) * 256) = v;
+        }
+    }
+}
+
 __device__ __forceinline__ void pool_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ void c1p_producer_bar() { asm volatile("bar.sync 2, 96;" ::: "memory"); }
 
@@ -348,6 +396,7 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             tc::cp_async_commit();
         };
         fetch_image(0, 0);
+        c1p_zero_row_pads(s16, pt);
         for (int it = 0; it < n_active; ++it) {
             const int b = it & 1;
             const int m = tab_m[it];
@@ -368,9 +417,9 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             fetch_image(it + 1, (it + 1) & 1);
             tc::cp_async_wait<2>();                                      // image it has landed
             c1p_producer_bar();
-            convert_rows(simg + b * 3072, lut, s16, pt, C1P_PRODUCERS);
+            c1p_convert_rows(simg + b * 3072, lut, s16, pt);
             c1p_producer_bar();
-            build_expanded_parity(s16, sE, pt, C1P_PRODUCERS);
+            c1p_build_expanded(s16, sE, pt);
             tc::cp_async_wait<1>();                                      // W1 and the parameters of image it
             tc::fence_async_smem();
             tc::mbar_arrive(&bars[b]);

@@ -504,6 +504,15 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             }
 #pragma unroll
             for (int co = 0; co < 32; ++co) best[co] += prm[co];
+            // pooled values and arg-max bytes go out first (256-bit stores: one full sector per lane)
+            if (valid && save_bwd) {
+                float *p1 = ws.p1 + (int64_t)slot * A1_SZ + pp * 32;
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8)
+                    tc::st_global_v8(p1 + c8 * 8, best[c8 * 8], best[c8 * 8 + 1], best[c8 * 8 + 2], best[c8 * 8 + 3],
+                                     best[c8 * 8 + 4], best[c8 * 8 + 5], best[c8 * 8 + 6], best[c8 * 8 + 7]);
+                tc::st_global_v8u(ws.idx1 + (int64_t)slot * A1_SZ + pp * 32, bi);
+            }
 
             // GroupNorm(2, 32): two passes over the registers (mean, then centred sum of squares)
             float s0 = 0.f, s1 = 0.f;
@@ -520,13 +529,12 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             const float inv_n = 1.f / 3600.f;
             const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
             float q0 = 0.f, q1 = 0.f;
-            if (valid) {
 #pragma unroll
-                for (int co = 0; co < 16; ++co) {
-                    const float d0 = best[co] - mean0, d1 = best[16 + co] - mean1;
-                    q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1);
-                }
+            for (int co = 0; co < 16; ++co) {                           // centre in place
+                best[co] -= mean0; best[16 + co] -= mean1;
+                q0 = fmaf(best[co], best[co], q0); q1 = fmaf(best[16 + co], best[16 + co], q1);
             }
+            if (!valid) { q0 = 0.f; q1 = 0.f; }
             q0 = warp_sum(q0); q1 = warp_sum(q1);
             if (lane == 0) { red2[warp * 2] = q0; red2[warp * 2 + 1] = q1; }
             pool_bar();
@@ -536,27 +544,17 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
 
             if (valid) {
-                if (save_bwd) {
-                    float4 *p1 = reinterpret_cast<float4 *>(ws.p1 + (int64_t)slot * A1_SZ + pp * 32);
+                float *a1 = ws.a1 + (int64_t)slot * A1_SZ + pp * 32;
 #pragma unroll
-                    for (int c4 = 0; c4 < 8; ++c4)
-                        p1[c4] = make_float4(best[c4 * 4], best[c4 * 4 + 1], best[c4 * 4 + 2], best[c4 * 4 + 3]);
-                    uint4 *ix = reinterpret_cast<uint4 *>(ws.idx1 + (int64_t)slot * A1_SZ + pp * 32);
-                    ix[0] = make_uint4(bi[0], bi[1], bi[2], bi[3]);
-                    ix[1] = make_uint4(bi[4], bi[5], bi[6], bi[7]);
-                }
-                float4 *a1 = reinterpret_cast<float4 *>(ws.a1 + (int64_t)slot * A1_SZ + pp * 32);
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    float o[8];
 #pragma unroll
-                for (int c4 = 0; c4 < 8; ++c4) {
-                    float o[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int co = c4 * 4 + e;
-                        const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
-                        const float v = (best[co] - mean) * rstd * prm[32 + co] + prm[64 + co];
+                    for (int e = 0; e < 8; ++e) {
+                        const int co = c8 * 8 + e;
+                        const float v = best[co] * (co < 16 ? rstd0 : rstd1) * prm[32 + co] + prm[64 + co];
                         o[e] = v > 0.f ? v : 0.f;
                     }
-                    a1[c4] = make_float4(o[0], o[1], o[2], o[3]);
+                    tc::st_global_v8(a1 + c8 * 8, o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]);
                 }
             }
             if (save_bwd && t == 0) {

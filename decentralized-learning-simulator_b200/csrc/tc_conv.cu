@@ -79,9 +79,11 @@ __device__ __forceinline__ void stage_items(int first, int n_items, int stride, 
             if (i < n_items) {
                 const float *src;
                 loc(i, src, dst[u]);
-                if (src) {
-                    a[u] = __ldg(reinterpret_cast<const float4 *>(src));
-                    b[u] = __ldg(reinterpret_cast<const float4 *>(src) + 1);
+                if (src) {                                        // one 256-bit load: a full 32-byte sector per lane
+                    float r[8];
+                    tc::ld_global_nc_v8(src, r);
+                    a[u] = make_float4(r[0], r[1], r[2], r[3]);
+                    b[u] = make_float4(r[4], r[5], r[6], r[7]);
                 }
             }
         }
@@ -272,14 +274,11 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
                 if (s < ns && oy < H && ox < H) {
                     float *dst = out + (int64_t)(slot0 + s) * (H * H * COUT) + (oy * H + ox) * COUT;
 #pragma unroll
-                    for (int j = 0; j < COUT; j += 4) {
-                        float4 v;
-                        v.x = __uint_as_float(r[j]) + sbias[j];
-                        v.y = __uint_as_float(r[j + 1]) + sbias[j + 1];
-                        v.z = __uint_as_float(r[j + 2]) + sbias[j + 2];
-                        v.w = __uint_as_float(r[j + 3]) + sbias[j + 3];
-                        *reinterpret_cast<float4 *>(dst + j) = v;
-                    }
+                    for (int j = 0; j < COUT; j += 8)
+                        tc::st_global_v8(dst + j, __uint_as_float(r[j]) + sbias[j], __uint_as_float(r[j + 1]) + sbias[j + 1],
+                                         __uint_as_float(r[j + 2]) + sbias[j + 2], __uint_as_float(r[j + 3]) + sbias[j + 3],
+                                         __uint_as_float(r[j + 4]) + sbias[j + 4], __uint_as_float(r[j + 5]) + sbias[j + 5],
+                                         __uint_as_float(r[j + 6]) + sbias[j + 6], __uint_as_float(r[j + 7]) + sbias[j + 7]);
                 }
             }
         }

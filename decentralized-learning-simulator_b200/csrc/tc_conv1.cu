@@ -573,15 +573,36 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
 //   dW1[co][c][ky][kx] = sum over samples and conv-output positions o of dc1[o][co] * P[o + (ky,kx)][c]
 // where dc1 is the gradient w.r.t. the conv1 output: the pooled gradient dp1 routed to the arg-max
 // position of every 3x3/2 window (overlapping windows add up).  Reduction (K) = the 1024 positions
-// of an image; A = the x-expanded image E (MN-major: M = (ky, 8 taps-channels), eight ky "chunks"
-// 32 entries apart, of which ky >= 5 are don't-care rows), B = dc1 as dense bf16 channel planes.
-// One CTA per node; warps 1-7 stage sample s+1 (expand image, scatter dp1) while warp 0 issues the
-// 128 MMAs (M=64, N=32, K=16) of sample s.
+// of an image; A = the x-expanded image E2[py][j][ox] (MN-major: the 16 chunks (ky, j) of a pixel are
+// 512 bytes apart, ky >= 5 are don't-care rows), B = dc1 as dense bf16 channel planes.
+// One CTA per node; warps 1-15 stage sample s+1 (expand image, scatter dp1) while warp 0 issues the
+// 64 MMAs (M=128, N=32, K=16) of sample s.
 // ------------------------------------------------------------------------------------------
 constexpr int DC_PLANE = 1024 * 16;
 constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
 constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128 + S16_BYTES;
 constexpr int C1W_THREADS = 512, C1W_PRODUCERS = 480;
+
+// E for the weight gradient: the two 8-element halves of a row are INTERLEAVED, E2[py][j][ox], so that the
+// (ky, j) operand chunks of one pixel are a uniform 512 bytes apart and a single M = 128 MMA covers all of them.
+__device__ __forceinline__ void build_expanded_il(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
+{
+    for (int i = t; i < 36 * 32 * 2; i += nthreads) {
+        const int ox = i & 31, j = (i >> 5) & 1, py = i >> 6;
+        const int y = py - 2;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (y >= 0 && y < 32) {
+            const int off = ox * 3 + 8 * j;
+            const uint32_t *rw = s16 + y * (ROW16 / 2) + (off >> 1);
+            const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
+            const uint32_t sh = (off & 1) ? 16u : 0u;
+            v.x = __funnelshift_r(w0, w1, sh); v.y = __funnelshift_r(w1, w2, sh);
+            v.z = __funnelshift_r(w2, w3, sh); v.w = __funnelshift_r(w3, w4, sh);
+            if (j) v.w &= 0x0000FFFFu;           // element 15 of the (kx, c) vector is the zero pad
+        }
+        *reinterpret_cast<uint4 *>(sE + i * 16) = v;          // ((py*2 + j)*32 + ox) == i
+    }
+}
 
 __device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 480;" ::: "memory"); }
 
@@ -636,7 +657,7 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
             if (id >= 0) {
                 convert_rows(simg, lut, s16, pt, C1W_PRODUCERS);
                 producer_sync();
-                build_expanded(s16, sE, pt, C1W_PRODUCERS);
+                build_expanded_il(s16, sE, pt, C1W_PRODUCERS);
                 const float *dp = ws.dp1 + (int64_t)slot * A1_SZ;
                 const uint8_t *ix = ws.idx1 + (int64_t)slot * A1_SZ;
                 // windows of one colour (py%2, px%2) never touch the same conv position, so the
@@ -682,21 +703,19 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
         }
     } else {
         const bool leader = tc::elect_one();          // warp-uniform loop, one elected lane issues
-        const uint32_t idesc = tc::instr_desc_bf16(64, 32, 1, 1);
+        const uint32_t idesc = tc::instr_desc_bf16(128, 32, 1, 1);
         uint32_t acc = 0;
         for (int s = 0; s < gs; ++s) {
             const int b = s & 1;
             tc::mbar_wait(&bars[b], (uint32_t)((s >> 1) & 1));
             tc::fence_after_sync();
             const uint32_t e_base = tc::smem_u32(smem + b * C1W_BUF);
-            const uint64_t ad0 = tc::smem_desc(e_base, 128, 512);                       // M chunks = ky, 32 entries apart
-            const uint64_t ad1 = tc::smem_desc(e_base + E_PLANE, 128, 512);
+            const uint64_t ad0 = tc::smem_desc(e_base, 128, 512);          // 16 M chunks (ky, j), 512 bytes apart
             const uint64_t bd0 = tc::smem_desc(e_base + 2 * E_PLANE, 128, DC_PLANE);
             if (leader) {
-#pragma unroll 4
-                for (int j = 0; j < 64; ++j) {
-                    tc::mma_f16(tmem, ad0 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
-                    tc::mma_f16(tmem + 32, ad1 + (uint64_t)(j * 16), bd0 + (uint64_t)(j * 16), idesc, acc);
+#pragma unroll 8
+                for (int k = 0; k < 64; ++k) {                              // 16 pixels: row k/2, half k%2
+                    tc::mma_f16(tmem, ad0 + (uint64_t)((k >> 1) * 64 + (k & 1) * 16), bd0 + (uint64_t)(k * 16), idesc, acc);
                     acc = 1;
                 }
                 tc::mma_commit(&bars[2 + b]);
@@ -711,19 +730,15 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
         tc::mbar_wait(&bars[4], 0);
         tc::fence_after_sync();
         float *G = ws.G + (int64_t)g * ws.ldg + OFF_W1;
-        const int mrow = warp * 16 + lane;                 // valid for lane < 16: row (ky, e) of the M = 64 tile
-        const int ky = mrow >> 3, e = mrow & 7;
+        const int mrow = warp * 32 + lane;                 // accumulator row = TMEM lane: chunk (ky, j) x 8 elements
+        const int ch = mrow >> 3, e = mrow & 7, ky = ch >> 1, q = 8 * (ch & 1) + e;
+        uint32_t r[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16), r);
+        tc::tmem_ld_wait();
+        if (ky < 5 && q < 15) {
+            const int kx = q / 3, c = q - kx * 3;
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            uint32_t r[32];
-            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(j * 32), r);
-            tc::tmem_ld_wait();
-            const int q = 8 * j + e;
-            if (lane < 16 && ky < 5 && q < 15) {
-                const int kx = q / 3, c = q - kx * 3;
-#pragma unroll
-                for (int co = 0; co < 32; ++co) G[co * 75 + c * 25 + ky * 5 + kx] = __uint_as_float(r[co]);
-            }
+            for (int co = 0; co < 32; ++co) G[co * 75 + c * 25 + ky * 5 + kx] = __uint_as_float(r[co]);
         }
     }
     tc::fence_before_sync();

@@ -53,4 +53,18 @@ __device__ __forceinline__ float block_sum(float v, float *red) {
     return t;
 }
 
+// Two block-wide sums with one pair of barriers (fixed reduction tree; `red` has >= 64 floats, blockDim <= 1024).
+__device__ __forceinline__ void block_sum2(float &a, float &b, float *red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    __syncthreads();
+    if (lane == 0) { red[warp * 2] = a; red[warp * 2 + 1] = b; }
+    __syncthreads();
+    float sa = 0.f, sb = 0.f;
+    for (int w = 0; w < nw; ++w) { sa += red[w * 2]; sb += red[w * 2 + 1]; }
+    a = sa;
+    b = sb;
+}
+
 }  // namespace dls

@@ -207,8 +207,8 @@ conv1_pool_gn_relu_kernel(Pass p, Workspace ws, int save_bwd)
     const float mean = grp ? mean1 : mean0;
     float q = 0.f;
     for (int e = t; e < A1_SZ; e += 256) { const float d = ps[e] - mean; q = fmaf(d, d, q); }
-    const float q0 = block_sum(grp == 0 ? q : 0.f, red);
-    const float q1 = block_sum(grp == 1 ? q : 0.f, red);
+    float q0 = grp == 0 ? q : 0.f, q1 = grp == 1 ? q : 0.f;
+    block_sum2(q0, q1, red);
     const float rstd0 = 1.f / sqrtf(q0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(q1 * inv_n + GN_EPS);
     const float rstd = grp ? rstd1 : rstd0;
     const float gam = row[OFF_G1W + ch], bet = row[OFF_G1B + ch];
@@ -238,7 +238,7 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
 {
     constexpr int SZ = H * H * C;
     __shared__ float cs[SZ];
-    __shared__ float red[32];
+    __shared__ float red[64];
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
     const int g = slot / p.gs;
@@ -248,15 +248,15 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
     const int ch = t % C, grp = ch >= (C / 2);
     float s = 0.f;
     for (int e = t; e < SZ; e += 256) { const float v = src[e]; cs[e] = v; s += v; }
-    const float sum0 = block_sum(grp == 0 ? s : 0.f, red);
-    const float sum1 = block_sum(grp == 1 ? s : 0.f, red);
+    float sum0 = grp == 0 ? s : 0.f, sum1 = grp == 1 ? s : 0.f;
+    block_sum2(sum0, sum1, red);
     const float inv_n = 1.f / (float)(SZ / 2);
     const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
     const float mean = grp ? mean1 : mean0;
     float q = 0.f;
     for (int e = t; e < SZ; e += 256) { const float d = cs[e] - mean; q = fmaf(d, d, q); }
-    const float q0 = block_sum(grp == 0 ? q : 0.f, red);
-    const float q1 = block_sum(grp == 1 ? q : 0.f, red);
+    float q0 = grp == 0 ? q : 0.f, q1 = grp == 1 ? q : 0.f;
+    block_sum2(q0, q1, red);
     const float rstd0 = 1.f / sqrtf(q0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(q1 * inv_n + GN_EPS);
     const float rstd = grp ? rstd1 : rstd0;
     const float gam = row[gw_off + ch], bet = row[gb_off + ch];
@@ -407,7 +407,7 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
 // overlapping windows in output-scan order (the order PyTorch's CPU kernel accumulates in).
 // ------------------------------------------------------------------------------------------
 template <int C, int H, int PH, bool POOL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (POOL && H == 15) ? 6 : 4)
 gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout,
                     const uint8_t *__restrict__ idx, const float *__restrict__ cpre,
                     const float *__restrict__ stats, float *__restrict__ dc, float *__restrict__ gnp,
@@ -451,30 +451,51 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
             __syncthreads();
         }
     }
+    // One pass over the sample: x-hat and the incoming gradient stay in registers between the statistics
+    // and the output pass (the pre-norm activations are read from memory once).  Block 1 (no pooling in
+    // front of the ReLU) re-derives the ReLU mask from x-hat instead of reading the activations back.
+    constexpr int NE = (SZ + 255) / 256;
+    constexpr bool KEEP = !(POOL && H == 15);              // block 2 needs its registers for occupancy: it re-reads
+    float xh[KEEP ? NE : 1];
+    const float bet = POOL ? 0.f : row[gw_off + C + ch];
     float s1 = 0.f, s2 = 0.f, dgam = 0.f, dbet = 0.f;     // 256 % C == 0: a thread only sees channel `ch`
-    for (int e = t; e < SZ; e += 256) {
-        const float d = POOL ? dg[e] : (as[e] > 0.f ? das[e] : 0.f);
-        dg[e] = d;
-        const float xhat = (cp[e] - mean) * rstd;
-        const float dxh = d * gam;
-        s1 += dxh;
-        s2 = fmaf(dxh, xhat, s2);
-        dgam = fmaf(d, xhat, dgam);
-        dbet += d;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const int e = t + k * 256;
+        if (KEEP) xh[k] = 0.f;
+        if (e < SZ) {
+            const float xhat = (cp[e] - mean) * rstd;
+            const float d = POOL ? dg[e] : ((xhat * gam + bet) > 0.f ? das[e] : 0.f);
+            if (KEEP) xh[k] = xhat;
+            if (!POOL) dg[e] = d;                          // own element: no barrier needed before the second pass
+            const float dxh = d * gam;
+            s1 += dxh;
+            s2 = fmaf(dxh, xhat, s2);
+            dgam = fmaf(d, xhat, dgam);
+            dbet += d;
+        }
     }
-    const float a0 = block_sum(grp == 0 ? s1 : 0.f, red);
-    const float a1 = block_sum(grp == 1 ? s1 : 0.f, red);
-    const float b0 = block_sum(grp == 0 ? s2 : 0.f, red);
-    const float b1 = block_sum(grp == 1 ? s2 : 0.f, red);
+    // the four group sums in one reduction: warp shuffles, then the eight warp partials in a fixed order
+    float r0 = warp_sum(grp == 0 ? s1 : 0.f), r1 = warp_sum(grp == 1 ? s1 : 0.f);
+    float r2 = warp_sum(grp == 0 ? s2 : 0.f), r3 = warp_sum(grp == 1 ? s2 : 0.f);
+    if ((t & 31) == 0) { red[(t >> 5) * 4] = r0; red[(t >> 5) * 4 + 1] = r1; red[(t >> 5) * 4 + 2] = r2; red[(t >> 5) * 4 + 3] = r3; }
+    __syncthreads();
+    float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { a0 += red[w * 4]; a1 += red[w * 4 + 1]; b0 += red[w * 4 + 2]; b1 += red[w * 4 + 3]; }
     const float inv_n = 1.f / (float)(SZ / 2);
     const float m1 = (grp ? a1 : a0) * inv_n, m2 = (grp ? b1 : b0) * inv_n;
     float *dst = dc + (int64_t)slot * SZ;
     float dbias = 0.f;                                     // sum of dc per channel = conv bias gradient partial
-    for (int e = t; e < SZ; e += 256) {
-        const float xhat = (cp[e] - mean) * rstd;
-        const float v = rstd * (dg[e] * gam - m1 - xhat * m2);
-        dst[e] = v;
-        dbias += v;
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const int e = t + k * 256;
+        if (e < SZ) {
+            const float xhat = KEEP ? xh[k] : (cp[e] - mean) * rstd;
+            const float v = rstd * (dg[e] * gam - m1 - xhat * m2);
+            dst[e] = v;
+            dbias += v;
+        }
     }
     // per-channel parameter-gradient partials of this sample: combine the 256/C threads of a channel
     // in a fixed order (dg is dead now: reuse it as scratch after a barrier)

@@ -23,36 +23,6 @@ namespace gnl {
 //   W2u [100][32][8] | W2ud [100][32][8] | W3u [100][64][8] | W3ud [200][32][8]
 constexpr int TCO_W2U = 0, TCO_W2UD = 25600, TCO_W3U = 51200, TCO_W3UD = 102400;
 
-__global__ void __launch_bounds__(256)
-prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t *model_active)
-{
-    const int m = blockIdx.y;
-    if (model_active && model_active[m] == 0) return;
-    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx;
-    __nv_bfloat16 *dst = prep + (int64_t)m * TC_PREP_ELEMS;
-    const int total = backward ? (TCO_W3UD + 51200) : TCO_W3UD;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        float v;
-        if (i < TCO_W2UD) {                       // W2u: k = tap*32 + ci ; [k/8][n=co][k%8]
-            const int e = i & 7, n = (i >> 3) & 31, kc = i >> 8, tap = kc >> 2, ci = (kc & 3) * 8 + e;
-            v = row[OFF_W2 + n * 800 + ci * 25 + tap];
-        } else if (i < TCO_W3U) {                 // W2ud: k = tap'*32 + co ; n = ci ; W2[co][ci][24-tap']
-            const int j = i - TCO_W2UD, e = j & 7, n = (j >> 3) & 31, kc = j >> 8, tap = kc >> 2,
-                      co = (kc & 3) * 8 + e;
-            v = row[OFF_W2 + co * 800 + n * 25 + (24 - tap)];
-        } else if (i < TCO_W3UD) {                // W3u: k = tap*32 + ci ; n = co (64)
-            const int j = i - TCO_W3U, e = j & 7, n = (j >> 3) & 63, kc = j >> 9, tap = kc >> 2,
-                      ci = (kc & 3) * 8 + e;
-            v = row[OFF_W3 + n * 800 + ci * 25 + tap];
-        } else {                                  // W3ud: k = tap'*64 + co ; n = ci (32) ; W3[co][ci][24-tap']
-            const int j = i - TCO_W3UD, e = j & 7, n = (j >> 3) & 31, kc = j >> 8, tap = kc >> 3,
-                      co = (kc & 7) * 8 + e;
-            v = row[OFF_W3 + co * 800 + n * 25 + (24 - tap)];
-        }
-        dst[i] = __float2bfloat16_rn(v);
-    }
-}
-
 __device__ __forceinline__ uint4 pack_bf16x8(const float4 a, const float4 b) {
     __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
     __nv_bfloat162 q2 = __floats2bfloat162_rn(b.x, b.y), q3 = __floats2bfloat162_rn(b.z, b.w);
@@ -60,6 +30,55 @@ __device__ __forceinline__ uint4 pack_bf16x8(const float4 a, const float4 b) {
     v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
     v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
     return v;
+}
+
+constexpr int PREP_ROW = 801;                 // padded source row (16 output channels x 800 weights) in shared memory
+constexpr int PREP_SMEM = 16 * PREP_ROW * 4;
+
+// One CTA = 16 output channels of conv2 (parts 0-1) or conv3 (parts 2-5) of one model: their 12800 fp32
+// weights are read once, coalesced, into shared memory and every 16-byte bf16 operand entry (8 k-values of
+// one n) is gathered from there and stored whole.
+//   W2u / W3u  : entry (kc = tap*4 + ci/8, n = co)          values e: W[co][ci = 8*(kc&3) + e][tap]
+//   W2ud / W3ud: entry (kc = tap'*(NCO/8) + co/8, n = ci)    values e: W[co = 8*(kc % (NCO/8)) + e][ci][24 - tap']
+__global__ void __launch_bounds__(256)
+prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t *model_active)
+{
+    extern __shared__ __align__(16) float wsrc[];                 // [16][PREP_ROW]
+    const int m = blockIdx.y, part = blockIdx.x, t = threadIdx.x;
+    if (model_active && model_active[m] == 0) return;
+    const bool l3 = part >= 2;
+    const int co0 = (l3 ? part - 2 : part) * 16, nco = l3 ? 64 : 32;
+    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx + (l3 ? OFF_W3 : OFF_W2) + co0 * 800;
+    __nv_bfloat16 *dst_u = prep + (int64_t)m * TC_PREP_ELEMS + (l3 ? TCO_W3U : TCO_W2U);
+    __nv_bfloat16 *dst_d = prep + (int64_t)m * TC_PREP_ELEMS + (l3 ? TCO_W3UD : TCO_W2UD);
+    for (int i = t; i < 16 * 200; i += 256) {                     // 16 rows of 800 floats, float4 loads
+        const int r = i / 200, c4 = i - r * 200;
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(row + r * 800) + c4);
+        float *d = wsrc + r * PREP_ROW + c4 * 4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+    __syncthreads();
+    const bool do_d = !l3 || backward;
+    for (int i = t; i < (do_d ? 3200 : 1600); i += 256) {
+        float v[8];
+        int64_t entry;
+        __nv_bfloat16 *dst;
+        if (i < 1600) {
+            const int nl = i & 15, kc = i >> 4, tap = kc >> 2, ci0 = (kc & 3) * 8;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = wsrc[nl * PREP_ROW + (ci0 + e) * 25 + tap];
+            entry = (int64_t)kc * nco + co0 + nl;
+            dst = dst_u;
+        } else {
+            const int j = i - 1600, n = j & 31, tg = j >> 5, cg = tg & 1, tap = tg >> 1;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = wsrc[(cg * 8 + e) * PREP_ROW + n * 25 + (24 - tap)];
+            entry = (int64_t)(tap * (nco / 8) + co0 / 8 + cg) * 32 + n;
+            dst = dst_d;
+        }
+        *reinterpret_cast<uint4 *>(dst + entry * 8) = pack_bf16x8(make_float4(v[0], v[1], v[2], v[3]),
+                                                                  make_float4(v[4], v[5], v[6], v[7]));
+    }
 }
 
 // Staging loop with U independent 32-byte global loads in flight per thread (the copies are
@@ -315,9 +334,15 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
 
 int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st)
 {
-    dim3 grid(8, p.n_models);
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(prep_weights_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    dim3 grid(6, p.n_models);
     const int32_t *active = p.gmodel ? nullptr : p.gcount;
-    prep_weights_tc_kernel<<<grid, 256, 0, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
+    prep_weights_tc_kernel<<<grid, 256, PREP_SMEM, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
                                                  active);
     DLS_LAUNCH_CHECK();
     return prep_w1_tc(p, ws, st);

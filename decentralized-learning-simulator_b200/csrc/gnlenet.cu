@@ -237,7 +237,7 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
                     uint8_t *__restrict__ idx, Pass p, int gw_off, int gb_off, int save_bwd)
 {
     constexpr int SZ = H * H * C;
-    __shared__ float cs[SZ];
+    __shared__ __align__(16) float cs[SZ];
     __shared__ float red[64];
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
@@ -245,22 +245,50 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
     int m;
     const float *row = model_row(p, g, m);
     const float *src = cpre + (int64_t)slot * SZ;
-    const int ch = t % C, grp = ch >= (C / 2);
+    // The sample is read once with 16-byte loads, all of them in flight together (the kernel is a
+    // stream over c: memory-level parallelism is what it needs), and stays in registers for both
+    // statistics passes.  A thread's four consecutive channels belong to one GroupNorm group.
+    static_assert(SZ % 4 == 0 && C % 4 == 0 && (C / 2) % 4 == 0, "float4 path");
+    constexpr int N4 = SZ / 4, NE4 = (N4 + 255) / 256;
+    const int c0 = (4 * t) % C, grp = c0 >= (C / 2);              // 1024 % C == 0: fixed channels per thread
+    float4 v[NE4];
+#pragma unroll
+    for (int k = 0; k < NE4; ++k) {
+        const int e4 = t + k * 256;
+        v[k] = e4 < N4 ? __ldg(reinterpret_cast<const float4 *>(src) + e4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     float s = 0.f;
-    for (int e = t; e < SZ; e += 256) { const float v = src[e]; cs[e] = v; s += v; }
+#pragma unroll
+    for (int k = 0; k < NE4; ++k) s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
     float sum0 = grp == 0 ? s : 0.f, sum1 = grp == 1 ? s : 0.f;
     block_sum2(sum0, sum1, red);
     const float inv_n = 1.f / (float)(SZ / 2);
     const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
     const float mean = grp ? mean1 : mean0;
     float q = 0.f;
-    for (int e = t; e < SZ; e += 256) { const float d = cs[e] - mean; q = fmaf(d, d, q); }
+#pragma unroll
+    for (int k = 0; k < NE4; ++k) {
+        if (t + k * 256 < N4) {
+            const float dx = v[k].x - mean, dy = v[k].y - mean, dz = v[k].z - mean, dw = v[k].w - mean;
+            q = fmaf(dx, dx, q); q = fmaf(dy, dy, q); q = fmaf(dz, dz, q); q = fmaf(dw, dw, q);
+        }
+    }
     float q0 = grp == 0 ? q : 0.f, q1 = grp == 1 ? q : 0.f;
     block_sum2(q0, q1, red);
     const float rstd0 = 1.f / sqrtf(q0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(q1 * inv_n + GN_EPS);
     const float rstd = grp ? rstd1 : rstd0;
-    const float gam = row[gw_off + ch], bet = row[gb_off + ch];
-    for (int e = t; e < SZ; e += 256) cs[e] = (cs[e] - mean) * rstd * gam + bet;
+    const float4 gam = *reinterpret_cast<const float4 *>(row + gw_off + c0);
+    const float4 bet = *reinterpret_cast<const float4 *>(row + gb_off + c0);
+#pragma unroll
+    for (int k = 0; k < NE4; ++k) {
+        const int e4 = t + k * 256;
+        if (e4 < N4) {
+            float4 o;
+            o.x = (v[k].x - mean) * rstd * gam.x + bet.x; o.y = (v[k].y - mean) * rstd * gam.y + bet.y;
+            o.z = (v[k].z - mean) * rstd * gam.z + bet.z; o.w = (v[k].w - mean) * rstd * gam.w + bet.w;
+            reinterpret_cast<float4 *>(cs)[e4] = o;
+        }
+    }
     __syncthreads();
     float *dst = aout + (int64_t)slot * (PH * PH * C);
     for (int o = t; o < PH * PH * C; o += 256) {

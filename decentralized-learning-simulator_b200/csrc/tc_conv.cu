@@ -85,7 +85,8 @@ prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t 
 // latency bound otherwise).  `loc(i, src, dst)` maps item i to its fp32 source (nullptr = zeros) and
 // its 16-byte shared-memory destination.
 template <int U, typename Loc>
-__device__ __forceinline__ void stage_items(int first, int n_items, int stride, Loc loc, int dup_off = 0) {
+__device__ __forceinline__ void stage_items(int first, int n_items, int stride, Loc loc, int dup_off = 0,
+                                            int dup_off2 = 0, int dup_off3 = 0) {
     for (int base = first; base < n_items; base += U * stride) {
         float4 a[U], b[U];
         uint8_t *dst[U];
@@ -111,7 +112,9 @@ __device__ __forceinline__ void stage_items(int first, int n_items, int stride, 
             if (dst[u]) {
                 const uint4 v = pack_bf16x8(a[u], b[u]);
                 *reinterpret_cast<uint4 *>(dst[u]) = v;
-                if (dup_off) *reinterpret_cast<uint4 *>(dst[u] + dup_off) = v;     // second (shifted) copy
+                if (dup_off) *reinterpret_cast<uint4 *>(dst[u] + dup_off) = v;     // shifted copies
+                if (dup_off2) *reinterpret_cast<uint4 *>(dst[u] + dup_off2) = v;
+                if (dup_off3) *reinterpret_cast<uint4 *>(dst[u] + dup_off3) = v;
             }
     }
 }
@@ -383,7 +386,7 @@ int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 // (13 x 32 fp32 TMEM columns); it walks over all samples of the node, double buffering the
 // staged planes: warps 1-7 stage chunk c+1 while one thread of warp 0 issues the MMAs of chunk c.
 // ==========================================================================================
-template <int COUT, int H, int SB, bool PAIR = false>
+template <int COUT, int H, int SB, bool PAIR = false, bool QUAD = false>
 struct WgradTcCfg {
     static constexpr int CIN = 32;
     using G = PlaneGeom<H>;
@@ -391,19 +394,20 @@ struct WgradTcCfg {
     // dY is zero at every origin past the last valid one of the chunk's last sample, so the reduction
     // stops there (H = 15, SB = 1: 253 origins -> 16 K steps)
     static constexpr int NVALID = (SB - 1) * NPS + G::NORIG;
-    static constexpr int KPIX = ((NVALID + 1 + 15) / 16) * 16;     // reduction length per chunk (+1: shifted copy)
+    static constexpr int DMAX = QUAD ? PP + 1 : 1;                  // largest shift of a dY copy
+    static constexpr int KPIX = ((NVALID + DMAX + 15) / 16) * 16;  // reduction length per chunk (+ the shifted copies)
     static constexpr int TAIL = ((G::TAIL + 7) / 8) * 8;
     static constexpr int FULL = (((SB - 1) * NPS + G::EXTENT + 7) / 8) * 8;
     static constexpr int NPD = KPIX, NPI = (KPIX + TAIL > FULL) ? KPIX + TAIL : FULL;
     static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
-    static constexpr int MROWS = PAIR ? 2 * COUT : 64;            // accumulator rows of one MMA
-    static constexpr int DPLANES = MROWS / 8;                      // 8-channel dY planes (PAIR: two shifted copies)
+    static constexpr int MROWS = QUAD ? 4 * COUT : (PAIR ? 2 * COUT : 64);   // accumulator rows of one MMA
+    static constexpr int DPLANES = MROWS / 8;                      // 8-channel dY planes (PAIR / QUAD: shifted copies)
     static constexpr int BUF = DPLANES * PLANE_D + 4 * PLANE_I;
     static constexpr int SMEM = 2 * BUF + 128;
     static constexpr int TAPS0 = 13;                                // taps of CTA half 0; half 1 gets 12
 };
 
-constexpr int WG_THREADS = 256;
+constexpr int WG_THREADS = 512;
 constexpr int WG_PRODUCERS = WG_THREADS - 32;
 
 // PAIR (COUT == 32): instead of four zero planes, rows 32..63 of the M = 64 operand hold a second
@@ -411,22 +415,26 @@ constexpr int WG_PRODUCERS = WG_THREADS - 32;
 // upper half of the accumulator is the weight gradient of the NEXT tap in x: one MMA yields taps
 // (ky,kx) and (ky,kx+1), 15 MMAs per K step cover all 25 taps (480 TMEM columns) and one CTA serves
 // a whole node.
-template <int COUT, int H, int SB, bool PAIR>
+// QUAD (COUT == 32): FOUR copies of dY — shifted by 0, 1, PP and PP + 1 pixels — fill an M = 128 operand, so one
+// MMA with the input shifted by (2a*PP + 2b) yields the 2x2 block of taps (2a + i, 2b + j): nine MMAs per K step
+// cover a 6x6 tap grid (the 5x5 kernel plus eleven discarded entries) instead of fifteen M = 64 MMAs.
+template <int COUT, int H, int SB, bool PAIR, bool QUAD>
 __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, Pass p, Workspace ws, int w_off)
 {
-    using C = WgradTcCfg<COUT, H, SB, PAIR>;
-    static_assert(!PAIR || (C::NPD > C::NVALID), "pair trick needs a spare plane entry");
+    using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD>;
+    static_assert(!QUAD || (PAIR && COUT == 32), "the quad variant is the four-copy form of the pair trick");
+    static_assert(!PAIR || (C::NPD >= C::NVALID + C::DMAX), "shifted copies need spare plane entries");
     static_assert(C::NPI >= C::FULL && C::NPI >= C::KPIX + C::TAIL, "input planes must hold every padded pixel of the chunk");
     static_assert(PAIR || COUT == 64, "without the pair trick the operand must have 64 real rows");
-    constexpr int NMMA = PAIR ? 15 : C::TAPS0;           // accumulator tiles (32 columns each) per CTA
+    constexpr int NMMA = QUAD ? 9 : (PAIR ? 15 : C::TAPS0);   // accumulator tiles (32 columns each) per CTA
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + 2 * C::BUF);   // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int g = PAIR ? blockIdx.x : (blockIdx.x >> 1), half = PAIR ? 0 : (blockIdx.x & 1);
     if (p.gcount[g] <= 0) return;
-    const int tap0 = half ? C::TAPS0 : 0, ntap = PAIR ? 15 : (half ? 25 - C::TAPS0 : C::TAPS0);
+    const int tap0 = half ? C::TAPS0 : 0, ntap = PAIR ? NMMA : (half ? 25 - C::TAPS0 : C::TAPS0);
     const int gs = p.gs, n_chunks = (gs + SB - 1) / SB;
 
     {   // zero both buffers once: padding borders, K tail and (conv2) the four unused dY planes stay zero
@@ -460,7 +468,8 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const bool ok = sl < gs && oy < H && ox < H && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
                 src = ok ? dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8 : nullptr;
                 dst = sD + ch * C::PLANE_D + pix * 16;
-            }, PAIR ? (COUT / 8) * C::PLANE_D + 16 : 0);
+            }, PAIR ? (COUT / 8) * C::PLANE_D + 16 : 0, QUAD ? 2 * (COUT / 8) * C::PLANE_D + C::PP * 16 : 0,
+               QUAD ? 3 * (COUT / 8) * C::PLANE_D + (C::PP + 1) * 16 : 0);
             stage_items<4>(pt, SB * H * H * 4, WG_PRODUCERS, [&](int i, const float *&src, uint8_t *&dst) {
                 const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
                 const int y = pix / H, x = pix - y * H;
@@ -481,7 +490,9 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         uint32_t tshift[NMMA];                       // tap shift in 16-byte units (registers: loops are unrolled)
 #pragma unroll
         for (int ti = 0; ti < NMMA; ++ti) {
-            if (PAIR) {
+            if (QUAD) {
+                tshift[ti] = (uint32_t)(2 * (ti / 3) * C::PP + 2 * (ti % 3));   // (ky, kx) = (0|2|4, 0|2|4)
+            } else if (PAIR) {
                 tshift[ti] = (uint32_t)((ti / 3) * C::PP + 2 * (ti % 3));       // (ky, kx = 0,2,4)
             } else {
                 const int tap = tap0 + (ti < ntap ? ti : 0);
@@ -513,32 +524,49 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
     }
     __syncwarp();
     // ------------------------------ epilogue: TMEM -> gradient row ------------------------------
+    // The accumulators are transposed through shared memory (the staging buffers are dead once the last MMA
+    // has completed) into the layout of the gradient row, [co][ci][tap] with a padded pitch of 801 floats per
+    // output channel, 32 output channels at a time, and leave the SM as coalesced stores.
+    static_assert(PAIR, "the transposed epilogue is written for the shifted-copy forms");
+    float *G = ws.G + (int64_t)g * ws.ldg + w_off;
+    float *sT = reinterpret_cast<float *>(smem);                   // [TR][801]
+    constexpr int TR = (32 * 801 * 4 <= 2 * C::BUF) ? 32 : 16;     // output channels per pass
+    static_assert(TR * 801 * 4 <= 2 * C::BUF, "transpose tile must fit in the staging buffers");
     if (warp < 4) {
         tc::mbar_wait(&bars[4], 0);
         tc::fence_after_sync();
-        float *G = ws.G + (int64_t)g * ws.ldg + w_off;
-        // an M = 64 accumulator keeps rows 16q .. 16q+15 in lanes 0..15 of TMEM quadrant q; M = 128 uses
-        // all 32 lanes of a quadrant (row = TMEM lane)
-        const int mrow = (C::MROWS == 128) ? (warp * 32 + lane) : (warp * 16 + lane);
-        const bool lane_ok = (C::MROWS == 128) || lane < 16;
-        for (int ti = 0; ti < ntap; ++ti) {
-            uint32_t r[32];
-            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ti * 32), r);
-            tc::tmem_ld_wait();
-            int co = mrow, tap = tap0 + ti;
-            bool ok = lane_ok && mrow < COUT;
-            if (PAIR) {
-                const int kx = 2 * (ti % 3) + (mrow >= COUT ? 1 : 0);   // upper rows: the tap one pixel to the right
-                co = mrow % COUT;
-                tap = (ti / 3) * 5 + kx;
-                ok = lane_ok && kx < 5;
-            }
-            if (ok) {
-                float *dst = G + (co * 32) * 25 + tap;
+    }
+    const int mrow = warp * 32 + lane;                             // M = 128: accumulator row = TMEM lane (warps 0-3)
+    for (int half = 0; half < COUT / TR; ++half) {
+        if (warp < 4) {
+            const int cp = mrow / COUT, co = mrow % COUT;          // shifted copy and output channel of this row
+            // tcgen05.ld is warp-wide: the branch around it is warp-uniform (the warp's 32 channels overlap this
+            // pass or not); only the shared-memory stores are per lane
+            if (((warp * 32) % COUT) / 32 == (half * TR) / 32) {
+                for (int ti = 0; ti < NMMA; ++ti) {
+                    int ky, kx;
+                    if (QUAD) { ky = 2 * (ti / 3) + (cp >> 1); kx = 2 * (ti % 3) + (cp & 1); }
+                    else      { ky = ti / 3;                   kx = 2 * (ti % 3) + cp; }
+                    if (ky < 5 && kx < 5) {                        // warp-uniform: a warp holds one copy
+                        uint32_t r[32];
+                        tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(ti * 32), r);
+                        tc::tmem_ld_wait();
+                        if (co / TR == half) {
+                            float *dst = sT + (co % TR) * 801 + ky * 5 + kx;
 #pragma unroll
-                for (int ci = 0; ci < 32; ++ci) dst[ci * 25] = __uint_as_float(r[ci]);
+                            for (int ci = 0; ci < 32; ++ci) dst[ci * 25] = __uint_as_float(r[ci]);
+                        }
+                    }
+                }
             }
         }
+        __syncthreads();
+        float *Gh = G + half * TR * 800;
+        for (int i = t; i < TR * 800; i += WG_THREADS) {
+            const int co = i / 800, rem = i - co * 800;
+            Gh[i] = sT[co * 801 + rem];
+        }
+        __syncthreads();
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -571,20 +599,20 @@ conv_bias_grad_kernel(const float *__restrict__ dY, Pass p, Workspace ws, int b_
     }
 }
 
-template <int COUT, int H, int SB, bool PAIR>
+template <int COUT, int H, int SB, bool PAIR, bool QUAD = false>
 static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Workspace &ws, int w_off, int b_off,
                            cudaStream_t st)
 {
-    using C = WgradTcCfg<COUT, H, SB, PAIR>;
+    using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD>;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB, PAIR>,
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) return (int)e;
         attr = true;
     }
-    conv_wgrad_tc_kernel<COUT, H, SB, PAIR><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(in, dY, p, ws,
-                                                                                                      w_off);
+    conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(in, dY, p,
+                                                                                                            ws, w_off);
     DLS_LAUNCH_CHECK();
     (void)b_off;      // the bias gradient comes from the per-sample partials of gn_block_bwd (gn_param_reduce)
     return 0;
@@ -592,7 +620,7 @@ static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Work
 
 int conv2_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_wgrad_tc<32, 15, 1, true>(ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2, st);
+    return launch_wgrad_tc<32, 15, 1, true, true>(ws.a1, ws.dc2, p, ws, OFF_W2, OFF_B2, st);
 }
 int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {

@@ -317,7 +317,9 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
 //   mode 1 (eval):  per-group loss sum and number of argmax hits (+ optional log-probs)
 // a3 is NHWC [hw][c]; the reference flattens C,H,W so feature f = c*9 + hw.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int CLS_THREADS = 576;       // one thread per classifier input feature in the weight-gradient loop
+
+__global__ void __launch_bounds__(CLS_THREADS)
 classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_logits, int logits_stride_model,
                   int logits_group0)
 {
@@ -331,11 +333,11 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
     if (cnt <= 0) return;
     int m;
     const float *row = model_row(p, g, m);
-    for (int i = t; i < NCLS * FEAT; i += 256) wfc[i] = row[OFF_FCW + i];
+    for (int i = t; i < NCLS * FEAT; i += CLS_THREADS) wfc[i] = row[OFF_FCW + i];
     if (t < NCLS) bfc[t] = row[OFF_FCB + t];
     __syncthreads();
     const int gs = p.gs;
-    for (int s = w; s < gs; s += 8) {
+    for (int s = w; s < gs; s += CLS_THREADS / 32) {
         const int slot = g * gs + s;
         if (p.img_idx[slot] < 0) { if (lane == 0) { lossv[s] = 0.f; hit[s] = 0; } continue; }
         const float *a3 = ws.a3 + (int64_t)slot * A3_SZ;
@@ -383,7 +385,7 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
     if (mode == 1) {
         if (out_logits) {
             // eval groups are (model, chunk of gs test samples); img_idx is the test sample id
-            for (int i = t; i < gs * NCLS; i += 256) {
+            for (int i = t; i < gs * NCLS; i += CLS_THREADS) {
                 const int s = i / NCLS, o = i - s * NCLS;
                 const int id = p.img_idx[g * gs + s];
                 if (id >= 0) out_logits[(int64_t)m * logits_stride_model + (int64_t)id * NCLS + o] = lg[s][o];
@@ -393,7 +395,7 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
     }
     // ---- train: gradients of the classifier and of its input ----
     float *G = ws.G + (int64_t)g * ws.ldg;
-    for (int i = t; i < A3_SZ; i += 256) {          // i indexes a3 NHWC; f = c*9+hw
+    for (int i = t; i < A3_SZ; i += CLS_THREADS) {          // i indexes a3 NHWC; f = c*9+hw
         const int hw = i >> 6, c = i & 63, f = c * 9 + hw;
         float acc[NCLS];
 #pragma unroll
@@ -413,7 +415,7 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
         for (int s = 0; s < gs; ++s) if (p.img_idx[g * gs + s] >= 0) b += lg[s][t];
         G[OFF_FCB + t] = b;
     }
-    for (int j = t; j < gs * A3_SZ; j += 256) {
+    for (int j = t; j < gs * A3_SZ; j += CLS_THREADS) {
         const int s = j / A3_SZ, i = j - s * A3_SZ;
         const int slot = g * gs + s;
         if (p.img_idx[slot] < 0) continue;
@@ -699,7 +701,7 @@ int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *o
                int logits_stride_model, cudaStream_t st)
 {
     if (p.gs > DLS_MAX_GROUP) return DLS_E_SHAPE;
-    classifier_kernel<<<p.n_groups, 256, 0, st>>>(p, ws, mode, loss_out, out_logits, logits_stride_model, 0);
+    classifier_kernel<<<p.n_groups, CLS_THREADS, 0, st>>>(p, ws, mode, loss_out, out_logits, logits_stride_model, 0);
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -433,9 +433,11 @@ def main():
                       "node_train_steps_per_s_train_only": node_steps_per_round / (train_t / 1e3)},
             "roofline": {"kernel": "agg_spmm (gossip aggregate wave)", "bound": "hbm", "achieved": agg_gbs,
                          "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": agg_gbs / pk["hbm_gbs"],
-                         # dram__bytes_read+write of agg_staged_uniform_kernel<16,9> from the ncu --set full
-                         # capture in profiles/ (N = 256 GNLeNet only; part of Y is still in L2 at kernel end)
-                         "traffic": 122480000 if (args.model == "gnlenet" and args.nodes_per_gpu == 256) else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of agg_staged_uniform_kernel<16,9>, one launch,
+                         # ncu --set full (profiles/r01_ncu_summary_final.md): 87.46 MB read + 36.01 MB written
+                         # (N = 256 GNLeNet only; most of Y is still in the 126 MB L2 when the kernel ends, so
+                         # DRAM traffic is BELOW the 174.8 MB algorithmic bytes: no wasted re-reads)
+                         "traffic": 123472128 if (args.model == "gnlenet" and args.nodes_per_gpu == 256) else None,
                          "peak_source": pk["source"] + " (burst copy bandwidth, MEASURED_PEAKS.json)"},
             "roofline_train": {"kernel": "train wave (all kernels of %d local steps)" % LOCAL_STEPS, "bound": "tensor",
                                "achieved": train_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",

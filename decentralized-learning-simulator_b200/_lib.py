@@ -26,6 +26,8 @@ SIGNATURES = {
     "dls_copy_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64,
                               c_void_p]),
     "dls_broadcast_row": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_void_p]),
+    "dls_gradient_update": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_float,
+                                    c_float, c_void_p]),
     "dls_train_workspace_bytes": (c_int64, [c_int32, c_int32, c_int32]),
     "dls_train_wave": (c_int, [c_int32, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32,

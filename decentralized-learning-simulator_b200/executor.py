@@ -24,11 +24,17 @@ from .util import MICROSECONDS
 class RowHandle:
     """Opaque result of a task: one row (slot) of the executor's stacked tensor.  This is what
     the API-compatible `train/aggregate/test` functions return in place of an `nn.Module`."""
-    __slots__ = ("executor", "slot")
+    __slots__ = ("executor", "slot", "grad_slot")
 
-    def __init__(self, executor: "WaveExecutor", slot: int):
+    def __init__(self, executor: "WaveExecutor", slot: int, grad_slot: Optional[int] = None):
         self.executor = executor
         self.slot = slot
+        self.grad_slot = grad_slot      # row holding `model.gradient` (results of compute_gradient tasks)
+
+    def gradient(self) -> Optional[np.ndarray]:
+        if self.grad_slot is None:
+            return None
+        return self.executor.X[self.grad_slot, :self.executor.layout.P].cpu().numpy()
 
     def numpy(self) -> np.ndarray:
         return self.executor.X[self.slot, :self.executor.layout.P].cpu().numpy()
@@ -182,6 +188,32 @@ class WaveExecutor:
         done = (cnt > 0).sum(axis=0).tolist()
         ti, tc = self._upload(idx, cnt)
         return ti, tc, done
+
+    def grad_wave(self, model_slots: Sequence[int], grad_slots: Sequence[int], peers: Sequence[int],
+                  rounds: Sequence[int]):
+        """`compute_gradient` for every task of the wave (dasklearn/functions.py:80-82 ->
+        ModelTrainer.train(gradient_only=True), model_trainer.py:60-124): mean-loss gradient of the first
+        minibatch of the (peer, round) loader order, written to row `grad_slots[t]`; models unchanged."""
+        T = len(model_slots)
+        if T == 0:
+            return
+        ls = self.settings.learning
+        mb_index, mb_count, _ = self.prepare_train(peers, rounds, [1] * T)
+        G = torch.empty((T, self.layout.ld), dtype=torch.float32, device=self.device)
+        K.grad_wave(self.layout, self.X, G, self._dev_i32(model_slots), self.dataset.images, self.dataset.labels,
+                    mb_index[0], mb_count[0], int(ls.batch_size), self.ws, precision=self.precision)
+        K.copy_rows(G, self.X, self._dev_i32(np.arange(T)), self._dev_i32(grad_slots), self.layout.P)
+        self.stats["grad_tasks"] = self.stats.get("grad_tasks", 0) + T
+
+    def gradient_update_wave(self, model_slots: Sequence[int], grad_slots: Sequence[int], out_slots: Sequence[int]):
+        """`gradient_update` for every task (functions.py:84-86 -> ModelTrainer.gradient_update,
+        model_trainer.py:133-143): one step of a fresh SGD optimizer, p <- p - lr * (g + wd * p)."""
+        if len(out_slots) == 0:
+            return
+        ls = self.settings.learning
+        K.gradient_update(self.X, self._dev_i32(model_slots), self._dev_i32(grad_slots), self._dev_i32(out_slots),
+                          self.layout.P, float(ls.learning_rate), float(ls.weight_decay))
+        self.stats["gradient_updates"] = self.stats.get("gradient_updates", 0) + len(out_slots)
 
     def aggregate_wave(self, model_slots: Sequence[Sequence[int]], out_slots: Sequence[int],
                        weights: Optional[Sequence[Optional[Sequence[float]]]] = None, variant: int = 0,

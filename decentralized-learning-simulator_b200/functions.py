@@ -1,6 +1,6 @@
-"""API-compatible task entry points: `train`, `aggregate`, `test` with the signature
-`f(settings, params) -> [result]` of the reference (dasklearn/functions.py:28-77, 89-106,
-109-133), looked up by name by the worker loop (`globals()[func_name]`, dasklearn/worker.py:27-31).
+"""API-compatible task entry points: `train`, `compute_gradient`, `gradient_update`, `aggregate`, `test`
+with the signature `f(settings, params) -> [result]` of the reference (dasklearn/functions.py:28-77,
+80-86, 89-106, 109-133), looked up by name by the worker loop (`globals()[func_name]`, dasklearn/worker.py:27-31).
 
 Differences that the DAG format hides: results are opaque `RowHandle`s (rows of the stacked
 HBM tensor) instead of `nn.Module`s, and the dataset is a device-resident `DeviceDataset`
@@ -48,8 +48,8 @@ def train(settings, params: Dict) -> List[RowHandle]:
     if isinstance(model, tuple):        # first round: the tuple (None, 0)  (functions.py:30-32)
         model = model[0]
     peer_id = params["peer"]
-    if params.get("compute_gradient") or params.get("gradient_model") is not None:
-        raise DlsError("compute_gradient / gradient_update tasks are not implemented by this executor")
+    compute_grad = params["compute_gradient"] if "compute_gradient" in params else False
+    gradient_model = params["gradient_model"] if "gradient_model" in params else None
     local_steps = params["local_steps"] if "local_steps" in params else settings.learning.local_steps
     ex = get_executor(settings)
     out = ex.alloc(1)[0]
@@ -58,8 +58,27 @@ def train(settings, params: Dict) -> List[RowHandle]:
         ex.init_rows([out])             # torch.manual_seed(seed); create_model(...)  (functions.py:46-48)
     else:
         ex.copy_rows([_slot_of(model, ex)], [out])   # the result is a detached copy (functions.py:64-70)
+    if gradient_model:                  # functions.py:54-55 -> ModelTrainer.gradient_update
+        if not isinstance(gradient_model, RowHandle) or gradient_model.grad_slot is None:
+            raise DlsError("gradient_model carries no gradient: %r" % (gradient_model,))
+        ex.gradient_update_wave([out], [gradient_model.grad_slot], [out])
+        return [RowHandle(ex, out)]
+    if compute_grad:                    # gradient_only=True: first minibatch, no optimizer step (model_trainer.py:122-124)
+        g = ex.alloc(1)[0]
+        ex.retain(g)
+        ex.grad_wave([out], [g], [peer_id], [params["round"]])
+        return [RowHandle(ex, out, g)]
     ex.train_wave([out], [peer_id], [params["round"]], [local_steps])
     return [RowHandle(ex, out)]
+
+
+def compute_gradient(settings, params: Dict) -> List[RowHandle]:
+    params["compute_gradient"] = True   # functions.py:80-82
+    return train(settings, params)
+
+
+def gradient_update(settings, params: Dict) -> List[RowHandle]:
+    return train(settings, params)      # functions.py:84-86
 
 
 def aggregate(settings, params: Dict) -> List[RowHandle]:
@@ -89,3 +108,5 @@ def test(settings, params: Dict) -> List[RowHandle]:
 def release(handle: RowHandle):
     """Give a row back to the pool (the reference relies on Python GC of nn.Modules)."""
     handle.executor.release(handle.slot)
+    if handle.grad_slot is not None:
+        handle.executor.release(handle.grad_slot)

@@ -52,6 +52,14 @@ def broadcast_row(src, Y, dst_rows, P: int):
     _lib.check(rc, "dls_broadcast_row")
 
 
+def gradient_update(X, p_rows, g_rows, out_rows, P: int, lr: float, wd: float):
+    """X[out] = X[p] - lr * (X[g] + wd * X[p]) row-wise (functions.gradient_update for every task of a wave)."""
+    _need_cuda(X, p_rows, g_rows, out_rows)
+    rc = _lib.lib().dls_gradient_update(X.data_ptr(), X.stride(0), _i32(p_rows).data_ptr(), _i32(g_rows).data_ptr(),
+                                        _i32(out_rows).data_ptr(), out_rows.numel(), P, float(lr), float(wd), _stream())
+    _lib.check(rc, "dls_gradient_update")
+
+
 class Workspace:
     """Caller-owned scratch buffer, grown on demand (torch allocates, the library never does)."""
 

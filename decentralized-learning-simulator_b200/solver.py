@@ -23,13 +23,13 @@ from ._lib import DlsError
 from .executor import RowHandle, WaveExecutor
 
 TRAIN_FUNCS = ("train",)
-SUPPORTED = ("train", "aggregate", "test")
+SUPPORTED = ("train", "aggregate", "test", "compute_gradient", "gradient_update")
 
 
 class Wave:
     __slots__ = ("level", "func", "names", "peers", "rounds", "times", "steps", "in_slots", "out_slots",
                  "model_slots", "weights", "init_slots", "copy_src", "copy_dst", "release_after", "prepared",
-                 "xchg")
+                 "xchg", "grad_slots")
 
     def __init__(self, level: int, func: str):
         self.level, self.func = level, func
@@ -48,6 +48,7 @@ class Wave:
         self.release_after: List[int] = []
         self.prepared = None
         self.xchg = None            # multi-GPU: halo exchange that precedes this wave
+        self.grad_slots: List[int] = []   # compute_gradient: row receiving the gradient; gradient_update: row read
 
 
 class BatchedSolver:
@@ -127,6 +128,25 @@ class BatchedSolver:
             return free.pop()
 
         self._value_slot = value_slot
+        grad_slot: Dict[Tuple[str, int], int] = {}        # outputs of compute_gradient tasks also carry a gradient row
+        self._grad_slot = grad_slot
+
+        def ref_of(r):
+            """Placeholders are (task name, output index) tuples; the AD-PSGD client also emits bare task
+            names (dasklearn/simulation/adpsgd/client.py:55-57, simulation/client.py:112-114)."""
+            if r is None:
+                return None
+            if isinstance(r, str):
+                return (r, 0)
+            r = tuple(r)
+            return None if r[0] is None else r
+
+        def consume(ref, pending):
+            """One consuming edge of `ref`: its model row and, if it has one, its gradient row."""
+            pending.append(value_slot[ref])
+            if ref in grad_slot:
+                pending.append(grad_slot[ref])
+
         for li, names in enumerate(self.levelise()):
             by_func: Dict[str, Wave] = {}
             # a level may hold two train tasks of one node only in malformed graphs; detect in executor
@@ -149,9 +169,7 @@ class BatchedSolver:
                 w.rounds.append(int(d.get("round", 0)))
                 w.times.append(int(d.get("time", 0)))
                 if func == "train":
-                    src = d["model"]
-                    if isinstance(src, tuple) and src[0] is None:
-                        src = None
+                    src = ref_of(d["model"])
                     w.steps.append(int(d.get("local_steps", default_steps)))
                     if src is None and peer in initial:
                         slot = initial[peer]                 # resume: train in place
@@ -160,21 +178,24 @@ class BatchedSolver:
                         slot = take()
                         w.init_slots.append(slot)
                     else:
-                        s_in = value_slot[tuple(src)]
+                        s_in = value_slot[src]
                         if sim_refs[s_in] == 1:              # sole consumer: train in place
                             slot = s_in
                             sim_refs[s_in] = 0
+                            if src in grad_slot:
+                                pending_release.append(grad_slot[src])
                         else:
                             slot = take()
                             w.copy_src.append(s_in)
                             w.copy_dst.append(slot)
-                            pending_release.append(s_in)
+                            consume(src, pending_release)
                     w.in_slots.append(slot)
                     w.out_slots.append(slot)
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
                 elif func == "aggregate":
-                    ms = [self._model_slot(tuple(m)) for m in d["models"]]
+                    refs = [tuple(m) for m in d["models"]]
+                    ms = [self._model_slot(m) for m in refs]
                     slot = take()
                     w.model_slots.append(ms)
                     w.weights.append(list(d["weights"]) if d.get("weights") else None)
@@ -182,13 +203,61 @@ class BatchedSolver:
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
                     pending_release.extend(x for x in ms if x >= 0)
+                    pending_release.extend(grad_slot[m] for m in refs if m in grad_slot)
+                elif func == "compute_gradient":
+                    # functions.py:80-82: forward/backward on the first minibatch, no optimizer step; the
+                    # result is the UNCHANGED model (an alias of the input row) plus a gradient row
+                    src = ref_of(d["model"])
+                    if src is None and peer in initial:
+                        s_in = initial[peer]
+                        sim_refs[s_in] -= 1
+                    elif src is None:
+                        s_in = take()
+                        w.init_slots.append(s_in)
+                    else:
+                        s_in = value_slot[src]
+                        consume(src, pending_release)        # after the alias below has taken its references
+                    g = take()
+                    w.in_slots.append(s_in)
+                    w.out_slots.append(s_in)
+                    w.grad_slots.append(g)
+                    sim_refs[s_in] += keep
+                    sim_refs[g] += keep
+                    value_slot[(name, 0)] = s_in
+                    grad_slot[(name, 0)] = g
+                elif func == "gradient_update":
+                    # functions.py:84-86: one step of a fresh SGD optimizer on `model` with the gradient
+                    # carried by `gradient_model` (possibly computed on an older model)
+                    src, gsrc = ref_of(d["model"]), ref_of(d["gradient_model"])
+                    if gsrc not in grad_slot:
+                        raise RuntimeError("gradient_update task %s: %r carries no gradient" % (name, gsrc))
+                    s_in, g = value_slot[src], grad_slot[gsrc]
+                    if sim_refs[s_in] == 1 and gsrc != src:  # sole consumer of the model: update in place
+                        slot = s_in
+                        sim_refs[s_in] = 0
+                        if src in grad_slot:
+                            pending_release.append(grad_slot[src])
+                    else:
+                        slot = take()
+                        consume(src, pending_release)
+                    if gsrc != src:                          # a second edge (simulation/client.py:112-115)
+                        consume(gsrc, pending_release)
+                    w.in_slots.append(s_in)
+                    w.out_slots.append(slot)
+                    w.grad_slots.append(g)
+                    sim_refs[slot] += keep
+                    value_slot[(name, 0)] = slot
                 else:                                        # test: identity on the model data path
-                    s_in = value_slot[tuple(d["model"])]
+                    src = ref_of(d["model"])
+                    s_in = value_slot[src]
                     w.in_slots.append(s_in)
                     w.out_slots.append(s_in)
                     sim_refs[s_in] += keep                   # alias first, then consume the input edge
                     value_slot[(name, 0)] = s_in
-                    pending_release.append(s_in)
+                    if src in grad_slot:                     # the alias keeps the gradient reachable too
+                        grad_slot[(name, 0)] = grad_slot[src]
+                        sim_refs[grad_slot[src]] += keep
+                    consume(src, pending_release)
                 if n_cons == 0:
                     self.sink_slots[name] = value_slot[(name, 0)]
             # inputs are released only after the whole level ran (their rows are read by this level)
@@ -198,7 +267,8 @@ class BatchedSolver:
                 sim_refs[s] = n
                 if n == 0:
                     free.append(s)
-            level_waves = [by_func[f] for f in ("train", "aggregate", "test") if f in by_func]
+            level_waves = [by_func[f] for f in ("train", "compute_gradient", "gradient_update", "aggregate", "test")
+                           if f in by_func]
             for w in level_waves:
                 self._end_level_wave(li, w)
             yield self._level_waves(li, level_waves)
@@ -271,6 +341,11 @@ class BatchedSolver:
         elif w.func == "aggregate":
             ex.aggregate_wave(w.model_slots, w.out_slots, w.weights, variant=self.agg_variant,
                               prepared=w.prepared)
+        elif w.func == "compute_gradient":
+            ex.init_rows(w.init_slots)
+            ex.grad_wave(w.in_slots, w.grad_slots, w.peers, w.rounds)
+        elif w.func == "gradient_update":
+            ex.gradient_update_wave(w.in_slots, w.grad_slots, w.out_slots)
         else:
             acc, loss = ex.test_wave(w.out_slots)
             for i, name in enumerate(w.names):

@@ -216,3 +216,51 @@ def gossip_dag(n: int, events: int, seed: int = 0) -> List[Dict]:
         model_of[j] = (aname, 0)
         age[j] = max(age[i], age[j])
     return list(tasks.values())
+
+
+def adpsgd_dag(n_pairs: int, rounds: int) -> List[Dict]:
+    """An AD-PSGD-shaped compute graph (dasklearn/simulation/adpsgd/client.py:32-110) in the reference's
+    task format: peers 2i are active, peers 2i+1 passive.  Every round a passive peer starts a
+    `compute_gradient` task on its model, exchanges models with its active partner while that gradient is
+    in flight (two fan-in-2 `aggregate` tasks), and then applies the now STALE gradient to the averaged
+    model with `gradient_update`; the active peer runs a `train` task on its averaged model.  As in the
+    reference, `gradient_model` is a bare task name while `model` is a (task name, index) placeholder
+    (simulation/client.py:106-115), and a `gradient_update` task has two input edges."""
+    tasks: Dict[str, Dict] = {}
+
+    def add(name, func, data, inputs):
+        tasks[name] = {"name": name, "func": func, "data": data, "inputs": list(inputs), "outputs": []}
+        for src, idx in inputs:
+            tasks[src]["outputs"].append((name, idx))
+
+    n = 2 * n_pairs
+    own: List[Tuple[str, int]] = []
+    cnt = {"train": 0, "cg": 0, "gu": 0, "agg": 0}
+
+    def name_of(kind, prefix):
+        cnt[kind] += 1
+        return "%s_%d" % (prefix, cnt[kind])
+
+    for i in range(n):                                         # everybody trains once from the initial model
+        t = name_of("train", "train")
+        add(t, "train", {"model": (None, 0), "round": 1, "time": 0, "peer": i}, [])
+        own.append((t, 0))
+    for r in range(2, rounds + 2):
+        for q in range(n_pairs):
+            a, p_ = 2 * q, 2 * q + 1
+            cg = name_of("cg", "compute_gradient")
+            add(cg, "compute_gradient", {"model": own[p_], "round": r, "time": r * 1000, "peer": p_, "local_steps": 1},
+                [own[p_]])
+            agg_p, agg_a = name_of("agg", "agg"), name_of("agg", "agg")
+            add(agg_p, "aggregate", {"models": [own[a], own[p_]], "round": r, "peer": p_, "weights": [0.5, 0.5]},
+                [own[a], own[p_]])
+            add(agg_a, "aggregate", {"models": [own[p_], own[a]], "round": r, "peer": a, "weights": [0.25, 0.75]},
+                [own[p_], own[a]])
+            gu = name_of("gu", "gradient_update")
+            add(gu, "gradient_update", {"model": (agg_p, 0), "round": r, "time": r * 1000 + 500, "peer": p_,
+                                        "gradient_model": cg}, [(agg_p, 0), (cg, 0)])
+            t = name_of("train", "train")
+            add(t, "train", {"model": (agg_a, 0), "round": r, "time": r * 1000 + 500, "peer": a, "local_steps": 2},
+                [(agg_a, 0)])
+            own[p_], own[a] = (gu, 0), (t, 0)
+    return list(tasks.values())

@@ -109,6 +109,15 @@ int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G, int64_t l
                   float *loss_out, int32_t precision, void *workspace, int64_t workspace_bytes,
                   void *stream);
 
+/* gradient_update wave — replaces N calls of functions.gradient_update -> ModelTrainer.gradient_update
+ * (dasklearn/functions.py:84-86, dasklearn/model_trainer.py:133-143): one step of a FRESH SGD optimizer
+ * with a supplied gradient, X[out_rows[r]] = X[p_rows[r]] - lr * (X[g_rows[r]] + wd * X[p_rows[r]])
+ * (single rounding, like torch's add_(buf, alpha=-lr)); gradients live in rows of X (as written by
+ * dls_grad_wave followed by dls_copy_rows).  out_rows[r] may equal p_rows[r] (in place); rows of
+ * different r must not alias.  The node's momentum rows are not touched. */
+int dls_gradient_update(float *X, int64_t ldx, const int32_t *p_rows, const int32_t *g_rows,
+                        const int32_t *out_rows, int32_t n_rows, int64_t P, float lr, float wd, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * test wave — replaces N calls of functions.test -> ModelEvaluator.evaluate_accuracy
  * (dasklearn/functions.py:109-133, dasklearn/model_evaluator.py:26-64).

@@ -241,6 +241,21 @@ def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarr
     return wl.grad.numpy().copy(), float(loss.detach())
 
 
+def gradient_update_task(row: np.ndarray, grad: np.ndarray, P: int, lr: float, wd: float) -> np.ndarray:
+    """`gradient_update` (dasklearn/functions.py:84-86 -> ModelTrainer.gradient_update,
+    model_trainer.py:133-143): ONE step of a FRESH torch.optim.SGD with the supplied gradient.  A fresh
+    optimizer has no momentum buffer: buf = g (+ wd*p), p <- p - lr*buf whatever the momentum setting.
+    torch's `p.add_(buf, alpha=-lr)` rounds once (fused); pinned by tests/golden/gradient_kat.npz."""
+    p = torch.from_numpy(np.array(row[:P], dtype=np.float32, copy=True))
+    g = torch.from_numpy(np.array(grad[:P], dtype=np.float32, copy=True))
+    if wd != 0:
+        g = g.add(p, alpha=wd)
+    p = p.add(g, alpha=-lr)
+    out = np.zeros_like(np.asarray(row, dtype=np.float32))
+    out[:P] = p.numpy()
+    return out
+
+
 # ---------------------------------------------------------------------------------------------
 # test — ModelEvaluator.evaluate_accuracy dasklearn/model_evaluator.py:26-64
 # ---------------------------------------------------------------------------------------------
@@ -317,9 +332,19 @@ def solve_dag(layout, serialized_tasks, part_images, part_labels, test_images, t
     tasks = {t["name"]: {"func": t["func"], "data": t["data"], "inputs": list(t["inputs"]),
                          "outputs": list(t["outputs"]), "resolved": 0} for t in serialized_tasks}
     values = {}
+    grads = {}
     moms = {}
     acc_rows = []
     sinks = {}
+
+    def _ref(r):
+        if r is None:
+            return None
+        if isinstance(r, str):
+            return (r, 0)
+        r = tuple(r)
+        return None if r[0] is None else r
+
     if init_row is None:
         init_row = initial_row(layout, seed)
     queue = [n for n, t in tasks.items() if not t["inputs"]]
@@ -329,8 +354,8 @@ def solve_dag(layout, serialized_tasks, part_images, part_labels, test_images, t
         d = t["data"]
         t0 = _time.perf_counter()
         if t["func"] == "train":
-            src = d["model"]
-            row = init_row if (src is None or src[0] is None) else values[tuple(src)]
+            src = _ref(d["model"])
+            row = init_row if src is None else values[src]
             peer, rnd = d["peer"], d["round"]
             steps = d.get("local_steps", local_steps)
             perm = minibatch_permutation(seed, peer, rnd, n_i)
@@ -348,9 +373,20 @@ def solve_dag(layout, serialized_tasks, part_images, part_labels, test_images, t
             rows = [values[tuple(m)] for m in d["models"]]
             res = fedavg_numpy(rows, d.get("weights"))
         elif t["func"] == "test":
-            res = values[tuple(d["model"])]
+            res = values[_ref(d["model"])]
             acc, loss, _ = evaluate(layout, res, test_images, test_labels)
             acc_rows.append((d["peer"], d["round"], d["time"], acc, loss))
+        elif t["func"] == "compute_gradient":                       # functions.py:80-82
+            src = _ref(d["model"])
+            res = init_row if src is None else values[src]
+            peer, rnd = d["peer"], d["round"]
+            perm = minibatch_permutation(seed, peer, rnd, n_i)[:batch]
+            g, _ = gradient_of(layout, res, part_images[peer][perm], part_labels[peer][perm])
+            gfull = np.zeros_like(np.asarray(res, dtype=np.float32))
+            gfull[:layout.P] = g
+            grads[(name, 0)] = gfull
+        elif t["func"] == "gradient_update":                        # functions.py:84-86
+            res = gradient_update_task(values[_ref(d["model"])], grads[_ref(d["gradient_model"])], layout.P, lr, wd)
         else:
             raise RuntimeError("Task function %s not found!" % t["func"])     # worker.py:26-27
         if timings is not None:

@@ -59,6 +59,20 @@ class OracleExecutor(WaveExecutor):
             self.moms[peer] = mom
             self.stats["train_steps"] += int((cnt[0] > 0).sum())
 
+    def grad_wave(self, model_slots, grad_slots, peers, rounds):
+        ls = self.settings.learning
+        for slot, g, peer, rnd in zip(model_slots, grad_slots, peers, rounds):
+            perm = synthetic.minibatch_permutation(self.settings.seed, peer, rnd, self.n_i)[:ls.batch_size]
+            grad, _ = O.gradient_of(self.layout, self.X[slot].numpy(), self.images[peer][perm], self.labels[peer][perm])
+            self.X[g] = 0
+            self.X[g, :self.layout.P] = torch.from_numpy(grad)
+
+    def gradient_update_wave(self, model_slots, grad_slots, out_slots):
+        ls = self.settings.learning
+        for s, g, o in zip(model_slots, grad_slots, out_slots):
+            self.X[o] = torch.from_numpy(O.gradient_update_task(self.X[s].numpy(), self.X[g].numpy(), self.layout.P,
+                                                                ls.learning_rate, ls.weight_decay))
+
     def aggregate_wave(self, model_slots, out_slots, weights=None, variant=0, prepared=None):
         rowptr, colidx, wval, src_rows, out_rows, n_src, _hint = prepared or self.prepare_aggregate(model_slots, out_slots,
                                                                                           weights)

@@ -196,6 +196,43 @@ def gen_train(work_dir):
     print("train_kat.npz written; __getitem__ calls:", ds.parts[peer].fetched)
 
 
+def gen_gradient(work_dir):
+    """AD-PSGD entry points (functions.py:80-86): `compute_gradient` = forward/backward on the first
+    minibatch of a fresh loader, no optimizer step, gradient attached to a copy of the unchanged model;
+    `gradient_update` = ONE step of a FRESH SGD optimizer (momentum buffer = g) with a supplied gradient."""
+    n_nodes, n_i, peer = 4, 80, 2
+    imgs, labs = synthetic.make_partitions(n_nodes, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(64, 32, 3, 10)
+    ds = SyntheticFederatedDataset(imgs, labs, timg, tlab)
+    reset_reference_globals(ds)
+    settings = make_settings(n_nodes, 2, 2, work_dir)
+    settings.data_dir = os.path.join(work_dir, "grad_kat")
+    os.makedirs(settings.data_dir, exist_ok=True)
+    ds.parts[peer].set_script(synthetic.minibatch_permutation(SEED, peer, 1, n_i))
+    gm = RF.compute_gradient(settings, {"model": (None, 0), "round": 1, "time": 0, "peer": peer})[0]
+    grad1 = np.concatenate([g.detach().cpu().numpy().reshape(-1) for g in gm.gradient]).astype(np.float32)
+    model_after_cg = flat(gm)
+    upd1 = flat(RF.gradient_update(settings, {"model": gm, "gradient_model": gm, "round": 1, "time": 0,
+                                              "peer": peer})[0])
+    # a stale gradient applied to a different (trained) model, then a second gradient at that model
+    ds.parts[peer].set_script(synthetic.minibatch_permutation(SEED, peer, 2, n_i))
+    trained = RF.train(settings, {"model": model_from_flat(upd1), "round": 2, "time": 0, "peer": peer})[0]
+    trained_flat = flat(trained)
+    gm_stale = model_from_flat(model_after_cg)
+    gm_stale.gradient = [g.clone() for g in gm.gradient]
+    upd2 = flat(RF.gradient_update(settings, {"model": trained, "gradient_model": gm_stale, "round": 2, "time": 0,
+                                              "peer": peer})[0])
+    ds.parts[peer].set_script(synthetic.minibatch_permutation(SEED, peer, 3, n_i))
+    gm2 = RF.compute_gradient(settings, {"model": model_from_flat(upd2), "round": 3, "time": 0, "peer": peer})[0]
+    grad2 = np.concatenate([g.detach().cpu().numpy().reshape(-1) for g in gm2.gradient]).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "gradient_kat.npz"), grad1=grad1, model_after_cg=model_after_cg, upd1=upd1,
+                        trained=trained_flat,
+                        upd2=upd2, grad2=grad2,
+                        meta=np.array(json.dumps({"n_nodes": n_nodes, "n_i": n_i, "peer": peer, "seed": SEED, "batch": 32,
+                                                  "lr": 0.002, "momentum": 0.9, "wd": 0.0, "torch": torch.__version__})))
+    print("gradient_kat.npz written; |g1| = %.6f, |g2| = %.6f" % (np.linalg.norm(grad1), np.linalg.norm(grad2)))
+
+
 def run_des(settings):
     loop = asyncio.new_event_loop()
     asyncio.set_event_loop(loop)
@@ -277,8 +314,12 @@ def gen_c2_dag(work_dir):
 if __name__ == "__main__":
     import tempfile
     wd = tempfile.mkdtemp(prefix="golden_")
+    if len(sys.argv) > 1 and sys.argv[1] == "gradient":          # only the AD-PSGD known-answer file
+        gen_gradient(wd)
+        sys.exit(0)
     gen_fedavg(wd)
     gen_init()
     gen_train(wd)
+    gen_gradient(wd)
     gen_dpsgd_mini(wd)
     gen_c2_dag(wd)

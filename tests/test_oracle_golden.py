@@ -95,3 +95,34 @@ def test_dpsgd_mini_full_solve(golden_dir):
     for peer, rnd, t_us, a, l in acc:
         line = "dpsgd,cifar10,iid,%g,%d,%d,%.2f,%f,%f" % (1, peer, rnd, t_us / 1e6, a, l)
         assert line in str(g["acc_csv"][peer])
+
+
+def test_compute_gradient_and_gradient_update_known_answers(golden_dir):
+    """AD-PSGD entry points, pinned to the reference's functions.compute_gradient / gradient_update
+    (tests/golden/make_golden.py gen_gradient): the gradient of the first scripted minibatch, and one
+    step of a fresh SGD optimizer (no momentum carry-over) with a fresh and with a stale gradient."""
+    t = np.load(os.path.join(golden_dir, "gradient_kat.npz"))
+    meta = json.loads(str(t["meta"]))
+    imgs, labs = synthetic.make_partitions(meta["n_nodes"], meta["n_i"], 32, 3, 10)
+    peer = meta["peer"]
+    init = O.initial_row(L, meta["seed"])
+    exact = torch.__version__ == meta["torch"]
+
+    def check(a, b):
+        if exact:
+            assert np.array_equal(a, b)
+        else:
+            np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-7)
+
+    assert np.array_equal(init[:L.P], t["model_after_cg"])             # compute_gradient leaves the model alone
+    perm = synthetic.minibatch_permutation(meta["seed"], peer, 1, meta["n_i"])[:32]
+    g1, _ = O.gradient_of(L, init, imgs[peer][perm], labs[peer][perm])
+    check(g1, t["grad1"])
+    check(O.gradient_update_task(init, t["grad1"], L.P, meta["lr"], meta["wd"])[:L.P], t["upd1"])
+    # momentum 0.9 is configured, yet the step is p - lr*g: the optimizer of gradient_update is fresh
+    assert np.array_equal(t["upd1"], (t["model_after_cg"].astype(np.float64)
+                                      - np.float64(np.float32(meta["lr"])) * t["grad1"].astype(np.float64)).astype(np.float32))
+    check(O.gradient_update_task(t["trained"], t["grad1"], L.P, meta["lr"], meta["wd"])[:L.P], t["upd2"])   # stale gradient
+    perm3 = synthetic.minibatch_permutation(meta["seed"], peer, 3, meta["n_i"])[:32]
+    g2, _ = O.gradient_of(L, t["upd2"], imgs[peer][perm3], labs[peer][perm3])
+    check(g2, t["grad2"])

@@ -140,3 +140,38 @@ def test_minibatch_index_partial_batches():
     idx, cnt = synthetic.minibatch_index(42, [3, 4], [1, 1], 48, 32, 5)
     assert cnt.tolist() == [[32, 16, 0, 0, 0], [32, 16, 0, 0, 0]]      # reference defect 14: 2 steps of 32+16
     assert (idx[0, 1, 16:] == -1).all() and sorted(idx[0, :2].ravel()[idx[0, :2].ravel() >= 0]) == list(range(48))
+
+
+def test_adpsgd_shaped_graph_solves_like_the_sequential_oracle(tmp_path):
+    """compute_gradient / gradient_update tasks (bare-name `gradient_model` references, stale gradients,
+    two input edges) through the batched solver with oracle arithmetic == the task-at-a-time oracle,
+    bit for bit, planned and streamed; every gradient row is returned to the pool."""
+    import sys
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from cpu_standin import OracleExecutor
+    from oracle import oracle as O
+    from dls_b200.layout import GNLENET as L
+    torch.set_num_threads(1)
+    n, n_i = 4, 40
+    dag = synthetic.adpsgd_dag(2, 2)
+    funcs = [t["func"] for t in dag]
+    assert funcs.count("compute_gradient") == 4 and funcs.count("gradient_update") == 4
+    assert all(len(t["inputs"]) == 2 for t in dag if t["func"] == "gradient_update")
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(16, 32, 3, 10)
+    st = SessionSettings(participants=n, seed=42, data_dir=str(tmp_path), learning=LearningSettings(0.002, 0.9, 0.0, 32, 2))
+    sinks, _ = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=42, batch=32, local_steps=2, lr=0.002, mu=0.9, wd=0.0,
+                           n_i=n_i, minibatch_permutation=synthetic.minibatch_permutation)
+    for streamed in (False, True):
+        ex = OracleExecutor(st, imgs, labs, timg, tlab, list(range(n)), n_i)
+        solver = BatchedSolver(ex, dag)
+        if not streamed:
+            solver.plan()
+        res = solver.run()
+        assert sorted(res) == sorted(sinks)
+        for name, row in sinks.items():
+            assert np.array_equal(ex.X[res[name][0].slot, :L.P].numpy(), row[:L.P]), name
+        # only the four sink rows stay referenced: gradient rows and intermediate models were released
+        assert int((ex.refs > 0).sum()) == 4
+        assert [w.func for w in solver.waves].count("compute_gradient") == 2

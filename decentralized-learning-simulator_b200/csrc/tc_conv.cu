@@ -182,7 +182,7 @@ conv_tc_kernel(const float *__restrict__ in, float *__restrict__ out, Pass p,
     uint64_t *bars = reinterpret_cast<uint64_t *>(sbias + COUT);       // full[2] empty[2] tfull[2] tempty[2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
 
-    const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
+    const int t = threadIdx.x, warp = tc::uniform_warp_idx();
     const int parts = (p.gs + spc - 1) / spc;
     const int g = blockIdx.x / parts, part = blockIdx.x - g * parts;
     if (p.gcount[g] <= 0) return;
@@ -573,31 +573,6 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
     if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
-// bias gradient db[co] = sum over the group's samples and pixels of dY (fixed order: deterministic)
-template <int COUT, int H>
-__global__ void __launch_bounds__(256)
-conv_bias_grad_kernel(const float *__restrict__ dY, Pass p, Workspace ws, int b_off)
-{
-    __shared__ float part[256];
-    const int g = blockIdx.x, t = threadIdx.x;
-    if (p.gcount[g] <= 0) return;
-    constexpr int ROWS = 256 / COUT;                       // pixel lanes per channel
-    const int co = t % COUT, r = t / COUT;
-    float s = 0.f;
-    for (int sl = 0; sl < p.gs; ++sl) {
-        const int slot = g * p.gs + sl;
-        if (p.img_idx[slot] < 0) continue;
-        const float *src = dY + (int64_t)slot * (H * H * COUT);
-        for (int pix = r; pix < H * H; pix += ROWS) s += src[pix * COUT + co];
-    }
-    part[t] = s;
-    __syncthreads();
-    if (t < COUT) {
-        float tot = 0.f;
-        for (int k = 0; k < ROWS; ++k) tot += part[k * COUT + t];
-        ws.G[(int64_t)g * ws.ldg + b_off + t] = tot;
-    }
-}
 
 template <int COUT, int H, int SB, bool PAIR, bool QUAD = false>
 static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Workspace &ws, int w_off, int b_off,

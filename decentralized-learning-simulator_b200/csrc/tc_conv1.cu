@@ -2,10 +2,11 @@
 // ReLU (block 1 of GNLeNet, dasklearn/models/cifar10.py:120-123), and its weight gradient.
 //
 // K = 75 is too thin for a channel-plane layout (3 channels), so the image is "x-expanded" in
-// shared memory: E[py][ox][16] = the 15 values (kx, c) of padded row py that output column ox needs
-// (+1 zero), as two 8-element planes.  For a fixed kernel row ky the A operand of 128 consecutive
-// output pixels (4 image rows) is then the plane shifted by ky*32 entries: 5 MMAs (M=128, N=32,
-// K=16) per tile, 8 tiles per image, no wasted rows.
+// shared memory: an entry (py, ox) = the 15 values (kx, c) of padded row py that output column ox needs
+// (+1 zero), as two 8-element halves j.  For a fixed kernel row ky the A operand of a run of output
+// pixels is then the expansion shifted by ky rows: one K = 16 MMA per kernel row.  The forward kernel
+// stores the entries in four parity planes (stride-2 windows for the fused pooling), the weight
+// gradient interleaves the halves (`E2[py][j][ox]`); both are described at their kernels below.
 #include "gnlenet.cuh"
 #include "tc_common.cuh"
 #include <cuda_bf16.h>
@@ -52,181 +53,6 @@ __device__ __forceinline__ void convert_rows(const uint8_t *simg, const __nv_bfl
     }
 }
 
-// Build the x-expanded bf16 planes E[j][py][ox][8] from the padded bf16 rows: entry (py, ox, j) is the
-// eight consecutive row elements starting at ox*3 + 8j (the 16th element of a pixel is a zero pad).
-__device__ __forceinline__ void build_expanded(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
-{
-    for (int i = t; i < 36 * 32 * 2; i += nthreads) {
-        const int j = i & 1, ox = (i >> 1) & 31, py = i >> 6;
-        const int y = py - 2;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (y >= 0 && y < 32) {
-            const int off = ox * 3 + 8 * j;
-            const uint32_t *rw = s16 + y * (ROW16 / 2) + (off >> 1);
-            const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
-            if (off & 1) {
-                v.x = __funnelshift_r(w0, w1, 16); v.y = __funnelshift_r(w1, w2, 16);
-                v.z = __funnelshift_r(w2, w3, 16); v.w = __funnelshift_r(w3, w4, 16);
-            } else {
-                v.x = w0; v.y = w1; v.z = w2; v.w = w3;
-            }
-            if (j) v.w &= 0x0000FFFFu;           // element 15 of the (kx, c) vector is the zero pad
-        }
-        *reinterpret_cast<uint4 *>(sE + j * E_PLANE + (py * 32 + ox) * 16) = v;
-    }
-}
-
-constexpr int RING_FLOATS = 8 * 32 * 33;       // conv rows ring: [8 rows][32 ox][32 co + 1 pad]
-constexpr int C1F_SMEM = 2 * E_PLANE + C1_W_BYTES + RING_FLOATS * 4 + 32 * 225 * 4 + 3072 + 512 + 32 * 4 + 32 * 4 + 64;
-
-constexpr int C1F_THREADS = 256;      // warps 0-3 drain TMEM; all warps expand the image, pool and normalise
-
-__global__ void __launch_bounds__(C1F_THREADS, 2)
-conv1_tc_kernel(Pass p, Workspace ws, int save_bwd)
-{
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *sE = smem;
-    uint8_t *sW = sE + 2 * E_PLANE;
-    float *ring = reinterpret_cast<float *>(sW + C1_W_BYTES);        // [8 rows][32 ox][33]: channel fastest, padded
-    float *ps = ring + RING_FLOATS;                                      // [32 co][225]
-    uint8_t *simg = reinterpret_cast<uint8_t *>(ps + 32 * 225);
-    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
-    float *sbias = reinterpret_cast<float *>(simg + 3072 + 512);
-    float *red = sbias + 32;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(red + 32);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2);
-    uint32_t *s16 = reinterpret_cast<uint32_t *>(ring);      // bf16 image rows; dead before the ring is first written
-
-    const int slot = blockIdx.x, t = threadIdx.x, warp = tc::uniform_warp_idx();
-    const int id = p.img_idx[slot];
-    if (id < 0) return;
-    const int g = slot / p.gs;
-    int m;
-    const float *row = model_row(p, g, m);
-
-    {
-        const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
-        for (int i = t; i < IMG_BYTES / 16; i += C1F_THREADS) reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
-        const uint4 *wsrc = reinterpret_cast<const uint4 *>(reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc) +
-                                                             (int64_t)m * TC_PREP_ELEMS + TCO_W1U);
-        for (int i = t; i < C1_W_BYTES / 16; i += C1F_THREADS) reinterpret_cast<uint4 *>(sW)[i] = __ldg(wsrc + i);
-        for (int i = t; i < 256; i += C1F_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
-        if (t < 32) sbias[t] = row[OFF_B1 + t];
-    }
-    if (t == 0) { tc::mbar_init(&bars[0], 1); tc::mbar_init(&bars[1], 1); tc::mbar_fence_init(); }
-    if (warp == 0) tc::tmem_alloc(tmem_slot, 64);
-    __syncthreads();
-    convert_rows(simg, lut, s16, t, C1F_THREADS);
-    __syncthreads();
-    build_expanded(s16, sE, t, C1F_THREADS);
-    tc::fence_async_smem();
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
-
-    const uint32_t tmem = *tmem_slot;
-    const uint32_t idesc = tc::instr_desc_bf16(128, 32, 0, 0);
-    const uint64_t ad0 = tc::smem_desc(tc::smem_u32(sE), E_PLANE, 128);
-    const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sW), 32 * 16, 128);
-    auto issue = [&](int k) {
-#pragma unroll
-        for (int ky = 0; ky < 5; ++ky)
-            tc::mma_f16(tmem + (uint32_t)((k & 1) * 32), ad0 + (uint64_t)(k * 128 + ky * 32),
-                        bd0 + (uint64_t)(ky * 2 * 32), idesc, ky > 0 ? 1u : 0u);
-        tc::mma_commit(&bars[k & 1]);
-    };
-    if (warp == 0) {                     // one elected lane of a converged warp issues (no per-MMA waterfall)
-        if (tc::elect_one()) { issue(0); issue(1); }
-        __syncwarp();
-    }
-
-    uint8_t *idx_out = ws.idx1 ? ws.idx1 + (int64_t)slot * A1_SZ : nullptr;
-    for (int k = 0; k < 8; ++k) {
-        if (warp < 4) {
-            tc::mbar_wait(&bars[k & 1], (uint32_t)((k >> 1) & 1));
-            tc::fence_after_sync();
-            uint32_t r[32];
-            tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)((k & 1) * 32), r);
-            tc::tmem_ld_wait();
-            // thread t holds conv output pixel (row 4k + t/32, ox = t%32), 32 channels
-            float *rw = ring + (((4 * k + (t >> 5)) & 7) * 32 + (t & 31)) * 33;     // stride 33: conflict free
-#pragma unroll
-            for (int co = 0; co < 32; ++co) rw[co] = __uint_as_float(r[co]) + sbias[co];
-        }
-        tc::fence_before_sync();
-        __syncthreads();
-        tc::fence_after_sync();
-        if (warp == 0 && k + 2 < 8) {
-            if (tc::elect_one()) issue(k + 2);
-            __syncwarp();
-        }
-        // pooled rows that are now complete: 2k-1 and 2k (3x3 windows, stride 2, first maximum wins).
-        // lane = channel; warp = (pooled row 0/1, quarter of the 15 columns): a thread loads the 3 x 9
-        // conv values its (up to) four adjacent windows share and scans each window in (dy, dx) order.
-        {
-            const int co = t & 31, pr = warp >> 2, qd = warp & 3, px0 = qd * 4, npx = (qd == 3) ? 3 : 4;
-            const int py = 2 * k - 1 + pr;
-            if (py >= 0) {
-                float v[3][9];
-#pragma unroll
-                for (int dy = 0; dy < 3; ++dy) {
-                    const float *rr = ring + ((((2 * py + dy) & 7) * 32 + 2 * px0) * 33) + co;
-#pragma unroll
-                    for (int x = 0; x < 9; ++x) v[dy][x] = (x <= 2 * npx) ? rr[x * 33] : 0.f;
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j < npx) {
-                        float best = -INFINITY;
-                        int bi = 0;
-#pragma unroll
-                        for (int dy = 0; dy < 3; ++dy)
-#pragma unroll
-                            for (int dx = 0; dx < 3; ++dx) {
-                                const float x = v[dy][2 * j + dx];
-                                if (x > best) { best = x; bi = dy * 3 + dx; }
-                            }
-                        const int pp = py * 15 + px0 + j;
-                        ps[co * 225 + pp] = best;
-                        if (save_bwd) idx_out[pp * 32 + co] = (uint8_t)bi;
-                    }
-                }
-            }
-        }
-        __syncthreads();
-    }
-    if (warp == 0) tc::tmem_dealloc(tmem, 64);
-
-    // GroupNorm(2, 32) over 16 channels x 225 pixels per group, then ReLU (ps is channel-major)
-    float s0 = 0.f, s1 = 0.f;
-    for (int e = t; e < A1_SZ; e += C1F_THREADS) { const float v = ps[e]; if (e < 3600) s0 += v; else s1 += v; }
-    const float sum0 = block_sum(s0, red), sum1 = block_sum(s1, red);
-    const float inv_n = 1.f / 3600.f;
-    const float mean0 = sum0 * inv_n, mean1 = sum1 * inv_n;
-    float q0 = 0.f, q1 = 0.f;
-    for (int e = t; e < A1_SZ; e += C1F_THREADS) {
-        const float d = ps[e] - (e < 3600 ? mean0 : mean1);
-        if (e < 3600) q0 = fmaf(d, d, q0); else q1 = fmaf(d, d, q1);
-    }
-    const float v0 = block_sum(q0, red), v1 = block_sum(q1, red);
-    const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
-    float *a1 = ws.a1 + (int64_t)slot * A1_SZ;
-    float *p1 = save_bwd ? ws.p1 + (int64_t)slot * A1_SZ : nullptr;
-    const int co = t & 31;
-    const float gam = row[OFF_G1W + co], bet = row[OFF_G1B + co];
-    const float mean = co < 16 ? mean0 : mean1, rstd = co < 16 ? rstd0 : rstd1;
-    for (int i = t; i < A1_SZ; i += C1F_THREADS) {          // i = pp*32 + co (256 % 32 == 0: co fixed per thread)
-        const float x = ps[co * 225 + (i >> 5)];
-        const float v = (x - mean) * rstd * gam + bet;
-        a1[i] = v > 0.f ? v : 0.f;
-        if (save_bwd) p1[i] = x;
-    }
-    if (save_bwd && t == 0) {
-        float *st = ws.st1 + (int64_t)slot * 4;
-        st[0] = mean0; st[1] = rstd0; st[2] = mean1; st[3] = rstd1;
-    }
-}
-
 // ------------------------------------------------------------------------------------------
 // conv1 + maxpool as NINE shifted convolutions (the forward kernel in use).
 //
@@ -251,29 +77,8 @@ constexpr int C1P_CAP = 256;                  // sample slots per CTA (descripto
 constexpr int C1P_SMEM = 2 * C1P_STAGE + S16_BYTES + 2 * 3072 + 512 + 4 * 96 * 4 + 4 * 16 * 4 +
                          (4 + 2 * C1P_SLOTS) * 8 + 64 + 4 * C1P_CAP * 4;
 
-// E entries into parity planes: plane ((pr&1)*2 + (ox&1))*2 + j, entry (pr>>1)*16 + (ox>>1).
-__device__ __forceinline__ void build_expanded_parity(const uint32_t *s16, uint8_t *sE, int t, int nthreads)
-{
-    for (int i = t; i < 36 * 32 * 2; i += nthreads) {
-        const int oxh = i & 15, j = (i >> 4) & 1, cpar = (i >> 5) & 1, pr = i >> 6;
-        const int ox = 2 * oxh + cpar, y = pr - 2;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (y >= 0 && y < 32) {
-            const int off = ox * 3 + 8 * j;
-            const uint32_t *rw = s16 + y * (ROW16 / 2) + (off >> 1);
-            const uint32_t w0 = rw[0], w1 = rw[1], w2 = rw[2], w3 = rw[3], w4 = rw[4];
-            if (off & 1) {
-                v.x = __funnelshift_r(w0, w1, 16); v.y = __funnelshift_r(w1, w2, 16);
-                v.z = __funnelshift_r(w2, w3, 16); v.w = __funnelshift_r(w3, w4, 16);
-            } else {
-                v.x = w0; v.y = w1; v.z = w2; v.w = w3;
-            }
-            if (j) v.w &= 0x0000FFFFu;
-        }
-        *reinterpret_cast<uint4 *>(sE + ((((pr & 1) * 2 + cpar) * 2 + j) * EP_PLANE) + ((pr >> 1) * 16 + oxh) * 16) = v;
-    }
-}
-
+// E entries go into parity planes: plane ((pr&1)*2 + (ox&1))*2 + j, entry (pr>>1)*16 + (ox>>1); an entry holds
+// the 8 consecutive bf16 of padded row pr-2 that start at element ox*3 + 8j (the 16th value of a pixel is a zero).
 // Producer-side versions for exactly C1P_PRODUCERS = 96 threads with loop-invariant index math.
 // The pad words of the bf16 rows are zeroed once per CTA (s16 is producer-private scratch).
 __device__ __forceinline__ void c1p_zero_row_pads(uint32_t *s16, int pt)
@@ -746,28 +551,6 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
     if (warp == 0) tc::tmem_dealloc(tmem, 64);
 }
 
-// bias gradient of conv1 = sum of the pooled gradient dp1 over samples and pixels (fixed order)
-__global__ void __launch_bounds__(256)
-conv1_bias_grad_kernel(Pass p, Workspace ws)
-{
-    __shared__ float part[256];
-    const int g = blockIdx.x, t = threadIdx.x, co = t & 31, r = t >> 5;
-    if (p.gcount[g] <= 0) return;
-    float s = 0.f;
-    for (int sl = 0; sl < p.gs; ++sl) {
-        const int slot = g * p.gs + sl;
-        if (p.img_idx[slot] < 0) continue;
-        const float *src = ws.dp1 + (int64_t)slot * A1_SZ;
-        for (int pix = r; pix < 225; pix += 8) s += src[pix * 32 + co];
-    }
-    part[t] = s;
-    __syncthreads();
-    if (t < 32) {
-        float tot = 0.f;
-        for (int k = 0; k < 8; ++k) tot += part[k * 32 + t];
-        ws.G[(int64_t)g * ws.ldg + OFF_B1 + t] = tot;
-    }
-}
 
 int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {

@@ -87,7 +87,13 @@ int forward(const Pass &p, Workspace &ws, bool save_for_backward, cudaStream_t s
 // mode 0: train (writes dlogits-derived grads: needs backward buffers); mode 1: eval
 int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *out_logits,
                int logits_stride_model, cudaStream_t st);
-int backward(const Pass &p, Workspace &ws, cudaStream_t st);
+// `lane` selects the side stream the weight-gradient kernels run on (two half-waves may be in flight)
+int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane = 0);
+
+// Streams owned by the library (created once per device): which = 0 / 2 weight-gradient side streams of
+// lane 0 / 1, which = 1 the main stream of lane 1 (second half of a split train wave).
+struct SideStream { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
+int side_stream(SideStream **out, int which);
 
 }  // namespace gnl
 }  // namespace dls

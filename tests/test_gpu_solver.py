@@ -299,3 +299,27 @@ def test_adpsgd_shaped_graph_on_gpu(cuda, tmp_path, precision):
         assert rel(res[name][0].numpy(), row[:L.P]) < tol, name
     assert ex.stats["grad_tasks"] == 12 and ex.stats["gradient_updates"] == 12
     assert int((ex.refs > 0).sum()) == n
+
+
+@pytest.mark.parametrize("precision", [0, 1])
+def test_split_train_wave_equals_small_waves(cuda, tmp_path, precision):
+    """A train wave with more tasks than SMs is run by the library as two lanes on two streams
+    (`split_point`, wave_api.cu); every task's result must be bit-identical to running the same tasks in
+    waves small enough to stay unsplit."""
+    n, n_i = 160, 64
+    st = SessionSettings(participants=n, seed=7, data_dir=str(tmp_path), learning=LearningSettings(0.002, 0.9, 0.0, 32, 2))
+    st.precision = precision
+    ds = DeviceDataset.synthetic(L, n, n_i, 16, cuda, seed=7)
+    out = []
+    for chunks in ([list(range(n))], [list(range(0, 70)), list(range(70, n))]):
+        ex = WaveExecutor(st, ds)
+        slots = ex.alloc(n)
+        ex.init_rows(slots)
+        for rnd in (1, 2):                                   # second round: momentum carried over
+            for peers in chunks:
+                ex.train_wave([slots[p] for p in peers], peers, [rnd] * len(peers))
+        torch.cuda.synchronize()
+        out.append((ex.X[slots, :L.P].cpu().numpy(), ex.M[:, :L.P].cpu().numpy()))
+    assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
+    assert np.array_equal(out[0][1].view(np.uint32), out[1][1].view(np.uint32))
+    assert not np.array_equal(out[0][0][0], out[0][0][159])

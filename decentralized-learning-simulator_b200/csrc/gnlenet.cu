@@ -710,14 +710,14 @@ int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *o
 // stream next to the data-gradient chain (fork/join with events): with one CTA per node, 256 nodes
 // fill 1.73 waves of the 148 SMs, and the other stream's kernels use the SMs an unfinished wave
 // leaves idle.  The side stream is created once per device and joined before this call returns.
-static SideStream g_side[64][3];      // per device: [0] wgrad side of lane 0, [1] lane-1 main stream, [2] wgrad side of lane 1
+static SideStream g_side[64][2 * MAX_LANES];   // per device: [2*lane] weight-gradient side stream, [2*lane+1] the lane's main stream
 
 int side_stream(SideStream **out, int which)
 {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
-    if (dev < 0 || dev >= 64 || which < 0 || which > 2) return DLS_E_TOO_BIG;
+    if (dev < 0 || dev >= 64 || which < 0 || which >= 2 * MAX_LANES) return DLS_E_TOO_BIG;
     SideStream &ss = g_side[dev][which];
     if (!ss.s) {
         if ((e = cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
@@ -737,7 +737,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane)
     const int S = p.n_groups * p.gs;
     if (ws.precision == 1) {
         SideStream *ss = nullptr;
-        if ((rc = side_stream(&ss, lane ? 2 : 0))) return rc;
+        if ((rc = side_stream(&ss, 2 * lane))) return rc;
         gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
                                                               ws.gnp, p, OFF_G3W, 192);
         DLS_LAUNCH_CHECK();

@@ -90,8 +90,9 @@ int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *o
 // `lane` selects the side stream the weight-gradient kernels run on (two half-waves may be in flight)
 int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane = 0);
 
-// Streams owned by the library (created once per device): which = 0 / 2 weight-gradient side streams of
-// lane 0 / 1, which = 1 the main stream of lane 1 (second half of a split train wave).
+// Streams owned by the library (created once per device): which = 2*lane is the weight-gradient side stream
+// of a lane, which = 2*lane + 1 the main stream of lanes >= 1 of a split train wave (lane 0 runs on the caller's).
+constexpr int MAX_LANES = 8;
 struct SideStream { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
 int side_stream(SideStream **out, int which);
 

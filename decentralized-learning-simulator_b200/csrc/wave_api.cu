@@ -1,5 +1,6 @@
 // C-ABI entry points for the train / grad / test waves (see include/dls_b200.h).
 #include "gnlenet.cuh"
+#include <cstdlib>
 
 namespace dls {
 namespace fem {
@@ -113,16 +114,52 @@ static int split_point(int n_tasks)
     return na < n_tasks ? na : n_tasks;
 }
 
+// Lanes of a train wave: default two (split_point); DLS_LANES=k (experiments) forces k equal lanes.
+static int lane_split(int n_tasks, int *lane_n, int *lane_off)
+{
+    int k = 0;
+    if (const char *e = getenv("DLS_LANE_SIZES")) {                   // experiments: explicit sizes "148,54,54"
+        int n = 0, off = 0;
+        const char *q = e;
+        while (*q && n < gnl::MAX_LANES && off < n_tasks) {
+            int v = atoi(q);
+            if (v <= 0) break;
+            if (off + v > n_tasks) v = n_tasks - off;
+            lane_n[n] = v; lane_off[n] = off; off += v; ++n;
+            while (*q && *q != ',') ++q;
+            if (*q == ',') ++q;
+        }
+        if (n > 0 && off == n_tasks) return n;
+    }
+    if (const char *e = getenv("DLS_LANES")) k = atoi(e);
+    if (k >= 1 && k <= gnl::MAX_LANES) {
+        if (k > n_tasks) k = n_tasks > 0 ? n_tasks : 1;
+        int off = 0;
+        for (int h = 0; h < k; ++h) {
+            lane_n[h] = n_tasks / k + (h < n_tasks % k ? 1 : 0);
+            lane_off[h] = off;
+            off += lane_n[h];
+        }
+        return k;
+    }
+    const int na = split_point(n_tasks);
+    lane_n[0] = na; lane_off[0] = 0;
+    if (na == n_tasks) return 1;
+    lane_n[1] = n_tasks - na; lane_off[1] = na;
+    return 2;
+}
+
 extern "C" int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int32_t batch)
 {
     if (n_tasks < 0 || batch <= 0 || batch > DLS_MAX_GROUP) return DLS_E_SHAPE;
     // sized for either precision (the tensor-core path adds bf16 weight copies)
     if (arch == DLS_ARCH_GNLENET) {
-        const int na = split_point(n_tasks), nb = n_tasks - na;
+        int lane_n[gnl::MAX_LANES], lane_off[gnl::MAX_LANES];
+        const int n_lanes = lane_split(n_tasks, lane_n, lane_off);
+        int64_t total = 0;
+        for (int h = 0; h < n_lanes; ++h) total += gnl::workspace_bytes(lane_n[h], batch, lane_n[h], true, true, 1);
         const int64_t whole = gnl::workspace_bytes(n_tasks, batch, n_tasks, true, true, 1);
-        const int64_t halves = gnl::workspace_bytes(na, batch, na, true, true, 1) +
-                               (nb > 0 ? gnl::workspace_bytes(nb, batch, nb, true, true, 1) : 0);
-        return whole > halves ? whole : halves;
+        return whole > total ? whole : total;
     }
     if (arch == DLS_ARCH_FEMNIST) return fem::train_workspace_bytes(n_tasks, batch, true);
     return DLS_E_SHAPE;
@@ -194,26 +231,34 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
     }
     if (n_tasks == 0 || n_steps == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    const int n_half[2] = {split_point(n_tasks), n_tasks - split_point(n_tasks)};
-    const int n_lanes = n_half[1] > 0 ? 2 : 1;
-    const int64_t bytes_a = gnl::workspace_bytes(n_half[0], batch, n_half[0], true, true, precision);
-    const int64_t bytes_b = n_lanes == 2 ? gnl::workspace_bytes(n_half[1], batch, n_half[1], true, true, precision) : 0;
-    if (workspace_bytes < bytes_a + bytes_b) return DLS_E_WS;
-    gnl::Workspace ws[2];
-    gnl::carve(ws[0], workspace, n_half[0], batch, n_half[0], true, true, precision);
-    cudaStream_t lane_stream[2] = {st, st};
-    gnl::SideStream *lane1 = nullptr;
-    if (n_lanes == 2) {
-        gnl::carve(ws[1], reinterpret_cast<char *>(workspace) + bytes_a, n_half[1], batch, n_half[1], true, true, precision);
-        if ((rc = gnl::side_stream(&lane1, 1))) return rc;
-        lane_stream[1] = lane1->s;
-        cudaError_t e = cudaEventRecord(lane1->fork, st);            // lane 1 starts after everything queued on `stream`
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(lane1->s, lane1->fork, 0);
-        if (e != cudaSuccess) return (int)e;
+    int lane_n[gnl::MAX_LANES], lane_off[gnl::MAX_LANES];
+    const int n_lanes = lane_split(n_tasks, lane_n, lane_off);
+    int64_t lane_bytes[gnl::MAX_LANES], total = 0;
+    for (int h = 0; h < n_lanes; ++h) {
+        lane_bytes[h] = gnl::workspace_bytes(lane_n[h], batch, lane_n[h], true, true, precision);
+        total += lane_bytes[h];
+    }
+    if (workspace_bytes < total) return DLS_E_WS;
+    gnl::Workspace ws[gnl::MAX_LANES];
+    cudaStream_t lane_stream[gnl::MAX_LANES];
+    gnl::SideStream *lane_ss[gnl::MAX_LANES];
+    char *wbase = reinterpret_cast<char *>(workspace);
+    for (int h = 0; h < n_lanes; ++h) {
+        gnl::carve(ws[h], wbase, lane_n[h], batch, lane_n[h], true, true, precision);
+        wbase += lane_bytes[h];
+        lane_stream[h] = st;
+        lane_ss[h] = nullptr;
+        if (h > 0) {                                                  // lanes >= 1 start after everything queued on `stream`
+            if ((rc = gnl::side_stream(&lane_ss[h], 2 * h + 1))) return rc;
+            lane_stream[h] = lane_ss[h]->s;
+            cudaError_t e = cudaEventRecord(lane_ss[h]->fork, st);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(lane_ss[h]->s, lane_ss[h]->fork, 0);
+            if (e != cudaSuccess) return (int)e;
+        }
     }
     for (int s = 0; s < n_steps; ++s) {
         for (int h = 0; h < n_lanes; ++h) {
-            const int off = h ? n_half[0] : 0, nt = n_half[h];
+            const int off = lane_off[h], nt = lane_n[h];
             cudaStream_t sh = lane_stream[h];
             gnl::Pass p;
             p.n_groups = nt; p.gs = batch; p.n_models = nt;
@@ -224,13 +269,14 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
             if ((rc = gnl_step(p, ws[h], loss_out ? loss_out + (int64_t)s * n_tasks + off : nullptr, sh, h))) return rc;
             dim3 grid(32, nt);
             sgd_update_kernel<<<grid, 256, 0, sh>>>(X, ldx, M, ldm, ws[h].G, ws[h].ldg, task_row + off, task_peer + off,
-                                                    (s == 0 && mom_first) ? mom_first + off : nullptr, p.gcount, gnl::P, lr, mu, wd);
+                                                    (s == 0 && mom_first) ? mom_first + off : nullptr, p.gcount, gnl::P,
+                                                    lr, mu, wd);
             DLS_LAUNCH_CHECK();
         }
     }
-    if (n_lanes == 2) {                                               // `stream` continues after both halves
-        cudaError_t e = cudaEventRecord(lane1->join, lane1->s);
-        if (e == cudaSuccess) e = cudaStreamWaitEvent(st, lane1->join, 0);
+    for (int h = 1; h < n_lanes; ++h) {                                // `stream` continues after every lane
+        cudaError_t e = cudaEventRecord(lane_ss[h]->join, lane_ss[h]->s);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(st, lane_ss[h]->join, 0);
         if (e != cudaSuccess) return (int)e;
     }
     return 0;

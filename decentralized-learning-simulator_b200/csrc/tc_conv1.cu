@@ -385,7 +385,9 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
 // ------------------------------------------------------------------------------------------
 constexpr int DC_PLANE = 1024 * 16;
 constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
-constexpr int C1W_SMEM = 2 * C1W_BUF + 3072 + 512 + 128 + S16_BYTES;
+constexpr int C1W_NB = 2;                     // operand buffers per CTA.  Tried: 1 buffer and two CTAs per SM (two nodes
+                                              // interleaving on one SM): 3 % slower end to end (64-register cap)
+constexpr int C1W_SMEM = C1W_NB * C1W_BUF + 3072 + 512 + 128 + S16_BYTES;
 constexpr int C1W_THREADS = 512, C1W_PRODUCERS = 480;
 
 // E for the weight gradient: the two 8-element halves of a row are INTERLEAVED, E2[py][j][ox], so that the
@@ -411,11 +413,11 @@ __device__ __forceinline__ void build_expanded_il(const uint32_t *s16, uint8_t *
 
 __device__ __forceinline__ void producer_sync() { asm volatile("bar.sync 1, 480;" ::: "memory"); }
 
-__global__ void __launch_bounds__(C1W_THREADS, 1)
+__global__ void __launch_bounds__(C1W_THREADS, C1W_NB == 1 ? 2 : 1)
 conv1_wgrad_tc_kernel(Pass p, Workspace ws)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *simg = smem + 2 * C1W_BUF;
+    uint8_t *simg = smem + C1W_NB * C1W_BUF;
     __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
     uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 3072 + 512);       // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
@@ -426,7 +428,7 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
     {
         uint4 *z = reinterpret_cast<uint4 *>(smem);
         const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-        for (int i = t; i < 2 * C1W_BUF / 16; i += C1W_THREADS) z[i] = zero;
+        for (int i = t; i < C1W_NB * C1W_BUF / 16; i += C1W_THREADS) z[i] = zero;
         for (int i = t; i < 256; i += C1W_THREADS) lut[i] = __float2bfloat16_rn(__fdiv_rn((float)i, 255.f));
     }
     if (t == 0) {
@@ -443,9 +445,9 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
     if (warp >= 1) {
         const int pt = t - 32;
         for (int s = 0; s < gs; ++s) {
-            const int b = s & 1, slot = g * gs + s;
+            const int b = s % C1W_NB, slot = g * gs + s;
             const int id = p.img_idx[slot];
-            if (s >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((s >> 1) - 1) & 1));
+            if (s >= C1W_NB) tc::mbar_wait(&bars[2 + b], (uint32_t)(((s / C1W_NB) - 1) & 1));
             uint8_t *sE = smem + b * C1W_BUF;
             uint8_t *sD = sE + 2 * E_PLANE;
             {
@@ -511,8 +513,8 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
         const uint32_t idesc = tc::instr_desc_bf16(128, 32, 1, 1);
         uint32_t acc = 0;
         for (int s = 0; s < gs; ++s) {
-            const int b = s & 1;
-            tc::mbar_wait(&bars[b], (uint32_t)((s >> 1) & 1));
+            const int b = s % C1W_NB;
+            tc::mbar_wait(&bars[b], (uint32_t)((s / C1W_NB) & 1));
             tc::fence_after_sync();
             const uint32_t e_base = tc::smem_u32(smem + b * C1W_BUF);
             const uint64_t ad0 = tc::smem_desc(e_base, 128, 512);          // 16 M chunks (ky, j), 512 bytes apart

@@ -353,7 +353,7 @@ int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st
 
 int conv2_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 32, 15, 3, true>(ws.a1, ws.c2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 32, 15, 1, true>(ws.a1, ws.c2, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                TCO_W2U, OFF_B2, st);
 }
 int conv3_fwd_tc(const Pass &p, Workspace &ws, cudaStream_t st)
@@ -368,7 +368,7 @@ int conv3_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 }
 int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    return launch_conv_tc<32, 32, 15, 3, false>(ws.dc2, ws.da1, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
+    return launch_conv_tc<32, 32, 15, 1, false>(ws.dc2, ws.da1, p, reinterpret_cast<const __nv_bfloat16 *>(ws.prep_tc),
                                                 TCO_W2UD, 0, st);
 }
 

@@ -97,48 +97,72 @@ class DistributedSolver(BatchedSolver):
         self.halo_bytes = 0
 
     # -- planning hooks ---------------------------------------------------------------------
+    # Every rank holds the whole task list, but its planning work is O(own tasks + cut edges): task owners
+    # and levels are looked up in dictionaries built once, and the rows this rank must SEND are found from
+    # the `outputs` lists of its own tasks instead of scanning every other rank's aggregate tasks.
     def _owner_of_task(self, name: str) -> int:
-        return int(self.owner_of[int(self.tasks[name]["data"]["peer"])])
+        return self._task_owner[name]
+
+    def levelise(self):
+        levels = super().levelise()
+        tasks, me = self.tasks, self.rank
+        owner_list = self.owner_of.tolist()       # plain ints: numpy scalar indexing is ~10x slower per lookup
+        self._task_owner = {name: owner_list[t["data"]["peer"]] for name, t in tasks.items()}
+        own = self._task_owner
+        level_of = {}
+        for li, names in enumerate(levels):
+            for n in names:
+                level_of[n] = li
+        remote = {}                               # level -> [(consumer rank, my value consumed there)], one per edge
+        for name, t in tasks.items():
+            if own[name] != me:
+                continue
+            for src, _ in t["inputs"]:
+                if own[src] != me and t["func"] != "aggregate":
+                    raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % name)
+            for cons, idx in t["outputs"]:
+                q = own[cons]
+                if q != me:
+                    if tasks[cons]["func"] != "aggregate":
+                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % cons)
+                    remote.setdefault(level_of[cons], []).append((q, (name, idx)))
+        self._remote = remote
+        # the base planner only looks at this rank's tasks
+        return [[n for n in names if own[n] == me] for names in levels]
+
+    def _halo_key(self, m):
+        return (int(self.tasks[m[0]]["data"]["peer"]), m[0], m[1])
 
     def _begin_level(self, level: int, names: List[str], pending_release: List[int]):
-        me = self.rank
-        recv: List[List[Tuple[str, int]]] = [[] for _ in range(self.world)]
-        send: List[List[int]] = [[] for _ in range(self.world)]
-        seen = set()
-        for name in names:
-            t = self.tasks[name]
-            q = self._owner_of_task(name)
+        me, own, tasks = self.rank, self._task_owner, self.tasks
+        recv = [set() for _ in range(self.world)]
+        send = [set() for _ in range(self.world)]
+        for name in names:                                    # this rank's tasks of the level
+            t = tasks[name]
             if t["func"] != "aggregate":
-                for src, _ in t["inputs"]:
-                    if self._owner_of_task(src) != q:
-                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate"
-                                           % name)
                 continue
             for m in t["data"]["models"]:
                 m = tuple(m)
-                r = self._owner_of_task(m[0])
-                if r == q:
-                    continue
-                if r == me:                                   # one reference per consuming remote task
-                    pending_release.append(self._value_slot[m])
-                if (q, m) in seen:
-                    continue
-                seen.add((q, m))
-                if q == me:
-                    recv[r].append(m)
-                if r == me:
-                    send[q].append(self._value_slot[m])
+                r = own[m[0]]
+                if r != me:
+                    recv[r].add(m)
+        for q, m in self._remote.get(level, ()):              # one reference per consuming remote task
+            pending_release.append(self._value_slot[m])
+            send[q].add(m)
+        # both ends order a (source rank -> destination rank) row list the same way: by producer peer, task, index
+        recv_l = [sorted(x, key=self._halo_key) for x in recv]
+        send_l = [sorted(x, key=self._halo_key) for x in send]
         self._halo_of = {}
         h = 0
         for r in range(self.world):                           # all_to_all output is ordered by source rank
-            for m in recv[r]:
+            for m in recv_l[r]:
                 self._halo_of[m] = h
                 h += 1
-        n_send = sum(len(x) for x in send)
+        n_send = sum(len(x) for x in send_l)
         if h or n_send:
-            self._level_xchg[level] = {"send_slots": [s for x in send for s in x],
-                                       "send_counts": [len(x) for x in send],
-                                       "recv_counts": [len(x) for x in recv]}
+            self._level_xchg[level] = {"send_slots": [self._value_slot[m] for x in send_l for m in x],
+                                       "send_counts": [len(x) for x in send_l],
+                                       "recv_counts": [len(x) for x in recv_l]}
             self.max_halo = max(self.max_halo, h)
             self.max_send = max(self.max_send, n_send)
 

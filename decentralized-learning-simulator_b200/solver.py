@@ -87,7 +87,8 @@ class BatchedSolver:
     def levelise(self) -> List[List[str]]:
         """Kahn wavefronts: level(t) = 1 + max(level of inputs).  Source tasks are level 0
         (`get_source_tasks`, dasklearn/tasks/dag.py:15-19)."""
-        indeg = {n: len(t["inputs"]) for n, t in self.tasks.items()}
+        tasks = self.tasks
+        indeg = {n: len(t["inputs"]) for n, t in tasks.items()}
         frontier = [n for n, d in indeg.items() if d == 0]
         levels: List[List[str]] = []
         seen = 0
@@ -95,11 +96,14 @@ class BatchedSolver:
             levels.append(frontier)
             seen += len(frontier)
             nxt: List[str] = []
+            push = nxt.append
             for n in frontier:
-                for m, _idx in self.tasks[n]["outputs"]:
-                    indeg[m] -= 1
-                    if indeg[m] == 0:
-                        nxt.append(m)
+                for out in tasks[n]["outputs"]:
+                    m = out[0]
+                    d = indeg[m] - 1
+                    indeg[m] = d
+                    if d == 0:
+                        push(m)
             frontier = nxt
         if seen != len(self.tasks):
             raise RuntimeError("compute graph has a cycle or dangling inputs (%d of %d tasks reachable)"

@@ -176,13 +176,16 @@ def test_functions_api_single_tasks(cuda, golden_dir, tmp_path):
     F.set_dataset(None)
 
 
-def test_c2_two_rounds_properties(cuda, golden_dir, tmp_path):
+@pytest.mark.parametrize("precision", [0, 1])
+def test_c2_two_rounds_properties(cuda, golden_dir, tmp_path, precision):
     """Full C2 size (256 nodes, k=8, reference DES graph): averaging must contract the spread
     of node models, preserve the network mean (doubly-stochastic mixing of a regular graph), and
-    be deterministic run to run."""
+    be deterministic run to run — on the fp32 path and on the tensor-core path (two lanes, side
+    streams, persistent pipelined kernels: any race between their roles would show up here)."""
     import gzip
     dag = pickle.load(gzip.open(os.path.join(golden_dir, "dpsgd_c2_dag.pkl.gz"), "rb"))
     st = SessionSettings(participants=256, data_dir=str(tmp_path), learning=LearningSettings(0.002, 0.9, 0.0, 32, 2))
+    st.precision = precision
     ds = DeviceDataset.synthetic(L, 256, 64, 64, cuda)
     finals = []
     for rep in range(2):

@@ -387,7 +387,7 @@ constexpr int DC_PLANE = 1024 * 16;
 constexpr int C1W_BUF = 2 * E_PLANE + 4 * DC_PLANE;
 constexpr int C1W_NB = 2;                     // operand buffers per CTA.  Tried: 1 buffer and two CTAs per SM (two nodes
                                               // interleaving on one SM): 3 % slower end to end (64-register cap)
-constexpr int C1W_SMEM = C1W_NB * C1W_BUF + 3072 + 512 + 128 + S16_BYTES;
+constexpr int C1W_SMEM = C1W_NB * C1W_BUF + 2 * 3072 + 512 + 128 + S16_BYTES + DLS_MAX_GROUP * 4;
 constexpr int C1W_THREADS = 512, C1W_PRODUCERS = 480;
 
 // E for the weight gradient: the two 8-element halves of a row are INTERLEAVED, E2[py][j][ox], so that the
@@ -418,13 +418,15 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *simg = smem + C1W_NB * C1W_BUF;
-    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 3072);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 3072 + 512);       // full[2], empty[2], done
+    __nv_bfloat16 *lut = reinterpret_cast<__nv_bfloat16 *>(simg + 2 * 3072);               // simg: two raw images
+    uint64_t *bars = reinterpret_cast<uint64_t *>(simg + 2 * 3072 + 512);   // full[2], empty[2], done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5);
-    uint32_t *s16 = reinterpret_cast<uint32_t *>(simg + 3072 + 512 + 128);
+    uint32_t *s16 = reinterpret_cast<uint32_t *>(simg + 2 * 3072 + 512 + 128);
+    int32_t *s_ids = reinterpret_cast<int32_t *>(reinterpret_cast<uint8_t *>(s16) + S16_BYTES);   // image id per sample
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int g = blockIdx.x, gs = p.gs;
     if (p.gcount[g] <= 0) return;
+    if (t < gs) s_ids[t] = p.img_idx[g * gs + t];          // no dependent global loads inside the sample loop
     {
         uint4 *z = reinterpret_cast<uint4 *>(smem);
         const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
@@ -444,9 +446,47 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
 
     if (warp >= 1) {
         const int pt = t - 32;
+        // Software pipeline over the samples of the node: the raw image bytes of sample s+1 (cp.async into a
+        // double buffer) and its pooled-gradient values / arg-max bytes (registers) are requested while
+        // sample s is expanded and scattered, so no global-memory latency sits between the producer barriers.
+        constexpr int MAXIT = 5;                            // ceil(8*8*32 / 480) windows of one colour per thread
+        float dv[4][MAXIT];
+        int ii[4][MAXIT];                                   // arg-max position 0..8, -1 = no window
+        auto fetch_image = [&](int s) {
+            if (s < gs) {
+                const int id = s_ids[s];
+                if (id >= 0 && pt < IMG_BYTES / 16)
+                    tc::cp_async16(simg + (s & 1) * 3072 + pt * 16, p.images + (int64_t)id * IMG_BYTES + pt * 16);
+            }
+            tc::cp_async_commit();
+        };
+        auto fetch_grad = [&](int s) {
+            const bool live = s < gs && s_ids[s < gs ? s : 0] >= 0;
+            const float *dp = ws.dp1 + (int64_t)(g * gs + (live ? s : 0)) * A1_SZ;
+            const uint8_t *ix = ws.idx1 + (int64_t)(g * gs + (live ? s : 0)) * A1_SZ;
+#pragma unroll
+            for (int colour = 0; colour < 4; ++colour) {
+                const int cy = colour >> 1, cx = colour & 1;
+                const int ny = (15 - cy + 1) / 2, nx = (15 - cx + 1) / 2;
+#pragma unroll
+                for (int it = 0; it < MAXIT; ++it) {
+                    const int i = pt + it * C1W_PRODUCERS;
+                    dv[colour][it] = 0.f;
+                    ii[colour][it] = -1;
+                    if (live && i < ny * nx * 32) {
+                        const int co = i & 31, w = i >> 5, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
+                        const int pp = py * 15 + px;
+                        dv[colour][it] = __ldg(dp + pp * 32 + co);
+                        ii[colour][it] = __ldg(ix + pp * 32 + co);
+                    }
+                }
+            }
+        };
+        fetch_image(0);
+        fetch_grad(0);
         for (int s = 0; s < gs; ++s) {
-            const int b = s % C1W_NB, slot = g * gs + s;
-            const int id = p.img_idx[slot];
+            const int b = s % C1W_NB;
+            const int id = s_ids[s];
             if (s >= C1W_NB) tc::mbar_wait(&bars[2 + b], (uint32_t)(((s / C1W_NB) - 1) & 1));
             uint8_t *sE = smem + b * C1W_BUF;
             uint8_t *sD = sE + 2 * E_PLANE;
@@ -454,60 +494,41 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
                 uint4 *z = reinterpret_cast<uint4 *>(sD);
                 const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
                 for (int i = pt; i < 4 * DC_PLANE / 16; i += C1W_PRODUCERS) z[i] = zero;
-                if (id >= 0) {
-                    const uint4 *src = reinterpret_cast<const uint4 *>(p.images + (int64_t)id * IMG_BYTES);
-                    for (int i = pt; i < IMG_BYTES / 16; i += C1W_PRODUCERS)
-                        reinterpret_cast<uint4 *>(simg)[i] = __ldg(src + i);
-                }
             }
+            tc::cp_async_wait<0>();                         // this sample's image bytes have landed
             producer_sync();
             if (id >= 0) {
-                convert_rows(simg, lut, s16, pt, C1W_PRODUCERS);
+                convert_rows(simg + (s & 1) * 3072, lut, s16, pt, C1W_PRODUCERS);
                 producer_sync();
+                fetch_image(s + 1);
                 build_expanded_il(s16, sE, pt, C1W_PRODUCERS);
-                const float *dp = ws.dp1 + (int64_t)slot * A1_SZ;
-                const uint8_t *ix = ws.idx1 + (int64_t)slot * A1_SZ;
                 // windows of one colour (py%2, px%2) never touch the same conv position, so the
                 // read-modify-write below is race free within a pass and the sum order is fixed
-                // all global loads of the four passes are issued up front (registers), so that the passes
-                // themselves only touch shared memory between the producer barriers
-                constexpr int MAXIT = 5;                        // ceil(8*8*32 / 480)
-                float dv[4][MAXIT];
-                uint32_t cell[4][MAXIT];                        // byte offset of the bf16 cell, 0xffffffff = none
 #pragma unroll
                 for (int colour = 0; colour < 4; ++colour) {
                     const int cy = colour >> 1, cx = colour & 1;
-                    const int ny = (15 - cy + 1) / 2, nx = (15 - cx + 1) / 2;
+                    const int nx = (15 - cx + 1) / 2;
 #pragma unroll
                     for (int it = 0; it < MAXIT; ++it) {
-                        const int i = pt + it * C1W_PRODUCERS;
-                        cell[colour][it] = 0xffffffffu;
-                        dv[colour][it] = 0.f;
-                        if (i < ny * nx * 32) {
+                        if (ii[colour][it] >= 0) {
+                            const int i = pt + it * C1W_PRODUCERS;
                             const int co = i & 31, w = i >> 5, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
-                            const int pp = py * 15 + px;
-                            dv[colour][it] = __ldg(dp + pp * 32 + co);
-                            const int ii = __ldg(ix + pp * 32 + co);
-                            const int o = (2 * py + ii / 3) * 32 + 2 * px + ii % 3;
-                            cell[colour][it] = (uint32_t)((co >> 3) * DC_PLANE + o * 16 + (co & 7) * 2);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int colour = 0; colour < 4; ++colour) {
-#pragma unroll
-                    for (int it = 0; it < MAXIT; ++it) {
-                        if (cell[colour][it] != 0xffffffffu) {
-                            __nv_bfloat16 *c = reinterpret_cast<__nv_bfloat16 *>(sD + cell[colour][it]);
+                            const int pos = ii[colour][it];
+                            const int o = (2 * py + pos / 3) * 32 + 2 * px + pos % 3;
+                            __nv_bfloat16 *c = reinterpret_cast<__nv_bfloat16 *>(sD + (co >> 3) * DC_PLANE + o * 16 + (co & 7) * 2);
                             *c = __float2bfloat16_rn(__bfloat162float(*c) + dv[colour][it]);
                         }
                     }
                     producer_sync();
                 }
+            } else {
+                fetch_image(s + 1);
             }
+            fetch_grad(s + 1);                              // in flight across the next sample's zero fill / expansion
             tc::fence_async_smem();
             asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc::smem_u32(&bars[b])) : "memory");
         }
+        tc::cp_async_wait<0>();
     } else {
         const bool leader = tc::elect_one();          // warp-uniform loop, one elected lane issues
         const uint32_t idesc = tc::instr_desc_bf16(128, 32, 1, 1);

@@ -436,6 +436,8 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
     if (p.gcount[g] <= 0) return;
     const int tap0 = half ? C::TAPS0 : 0, ntap = PAIR ? NMMA : (half ? 25 - C::TAPS0 : C::TAPS0);
     const int gs = p.gs, n_chunks = (gs + SB - 1) / SB;
+    __shared__ uint8_t s_live[DLS_MAX_GROUP];                 // sample slot holds an image (no dependent global loads
+    if (t < gs) s_live[t] = p.img_idx[g * gs + t] >= 0;       // in the staging loops)
 
     {   // zero both buffers once: padding borders, K tail and (conv2) the four unused dY planes stay zero
         uint4 *z = reinterpret_cast<uint4 *>(smem);
@@ -465,7 +467,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const int pix = i / (COUT / 8), ch = i - pix * (COUT / 8);
                 const int s = pix / C::NPS, loc = pix - s * C::NPS, oy = loc / C::PP, ox = loc - oy * C::PP;
                 const int sl = c * SB + s;
-                const bool ok = sl < gs && oy < H && ox < H && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
+                const bool ok = sl < gs && oy < H && ox < H && s_live[sl < gs ? sl : 0];
                 src = ok ? dY + (int64_t)(g * gs + sl) * (H * H * COUT) + (oy * H + ox) * COUT + ch * 8 : nullptr;
                 dst = sD + ch * C::PLANE_D + pix * 16;
             }, PAIR ? (COUT / 8) * C::PLANE_D + 16 : 0, QUAD ? 2 * (COUT / 8) * C::PLANE_D + C::PP * 16 : 0,
@@ -474,7 +476,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 const int ch = i & 3, q = i >> 2, s = q / (H * H), pix = q - s * (H * H);
                 const int y = pix / H, x = pix - y * H;
                 const int sl = c * SB + s;
-                const bool ok = sl < gs && p.img_idx[g * gs + (sl < gs ? sl : 0)] >= 0;
+                const bool ok = sl < gs && s_live[sl < gs ? sl : 0];
                 src = ok ? in + (int64_t)(g * gs + sl) * (H * H * 32) + pix * 32 + ch * 8 : nullptr;
                 dst = sI + ch * C::PLANE_I + (s * C::NPS + (y + 2) * C::PP + (x + 2)) * 16;
             });

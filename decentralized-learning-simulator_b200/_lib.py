@@ -21,6 +21,8 @@ SIGNATURES = {
     "dls_version": (c_int, []),
     "dls_build_info": (c_char_p, []),
     "dls_launch_count": (c_int64, []),
+    "dls_tune": (c_int, [c_int32, c_int32]),
+    "dls_agg_variant_fits": (c_int, [c_int32, c_int32, c_int32, c_int32]),
     "dls_agg_spmm_f32": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int64, c_int32, c_void_p]),
     "dls_copy_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64,

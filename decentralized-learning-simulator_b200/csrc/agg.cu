@@ -15,7 +15,6 @@
 //                (cp.async, double buffered); every output row is formed from shared memory, so
 //                HBM and L2 see each X element exactly once.
 #include "common.cuh"
-#include <stdlib.h>
 
 namespace dls {
 
@@ -378,42 +377,28 @@ copy_rows_kernel(const float *__restrict__ X, int64_t ldx, float *__restrict__ Y
         reinterpret_cast<float4 *>(yd)[c] = reinterpret_cast<const float4 *>(xs)[c];
 }
 
-static int g_num_sms = 0;
-static int g_max_smem_optin = 0;
-static int device_props() {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return (int)e;
-        e = cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return (int)e;
-        e = cudaDeviceGetAttribute(&g_max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        if (e != cudaSuccess) return (int)e;
-    }
-    return 0;
-}
-
-struct StagedPlan { int tw4; int stages; bool csr_smem; size_t smem; };
+struct StagedPlan { int tw4; int stages; bool csr_smem; size_t smem; int sms; };
 
 // Largest tile width that still leaves >= 3 stages (2 loads in flight while one tile is consumed).
-static bool plan_staged(int n_rows, int n_src, int n_ent, StagedPlan &pl)
+static bool plan_staged(const DeviceInfo &di, int n_rows, int n_src, int n_ent, StagedPlan &pl)
 {
-    const int64_t budget = g_max_smem_optin - 256;
+    pl.sms = di.sms;
+    const int64_t budget = di.smem_optin - 256;
     const int64_t rowptr_bytes = (int64_t)((n_rows + 1 + 3) & ~3) * 4;
     const int64_t csr_bytes = ((int64_t)n_ent + n_rows) * 8;   // room for the uniform kernel's pair padding
-    const char *e_tw = getenv("DLS_AGG_TW4"), *e_st = getenv("DLS_AGG_STAGES");   // tuning overrides
+    const int e_tw = tune_value(TUNE_AGG_TW4), e_st = tune_value(TUNE_AGG_STAGES);   // dls_tune() overrides (0 = auto)
     const int cand[3] = {16, 8, 4};
     for (int pass = 0; pass < 2; ++pass) {
         const int min_stages = pass == 0 ? 3 : 2;
         for (int ci = 0; ci < 3; ++ci) {
             const int tw4 = cand[ci];
-            if (e_tw && atoi(e_tw) != tw4) continue;
+            if (e_tw && e_tw != tw4) continue;
             const int64_t stage = (int64_t)n_src * tw4 * 16;
             for (int csr = 1; csr >= 0; --csr) {
                 const int64_t fixed = rowptr_bytes + (csr ? csr_bytes : 0);
                 int64_t st = (budget - fixed) / stage;
                 if (st > STG_MAX_STAGES) st = STG_MAX_STAGES;
-                if (e_st && atoi(e_st) <= st) st = atoi(e_st);
+                if (e_st && e_st <= st) st = e_st;
                 if (st >= min_stages) {
                     pl.tw4 = tw4; pl.stages = (int)st; pl.csr_smem = csr != 0;
                     pl.smem = (size_t)(st * stage + fixed);
@@ -435,7 +420,7 @@ static int launch_staged_t(const StagedPlan &pl, const float *X, int64_t ldx, fl
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return (int)e;
     const int n_tiles = (int)((P4 + TW4 - 1) / TW4);
-    const int rounds = (n_tiles + g_num_sms - 1) / g_num_sms;
+    const int rounds = (n_tiles + pl.sms - 1) / pl.sms;
     const int grid = (n_tiles + rounds - 1) / rounds;          // same critical path, fewer idle tails
     agg_staged_kernel<TW4, CSR_SMEM><<<grid, STG_THREADS, pl.smem, st>>>(
         X, ldx, Y, ldy, rowptr, colidx, wval, src_rows, out_rows, n_rows, n_src, n_ent, P4, n_tiles, pl.stages,
@@ -454,7 +439,7 @@ static int launch_uniform_t(const StagedPlan &pl, const float *X, int64_t ldx, f
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return (int)e;
     const int n_tiles = (int)((P4 + TW4 - 1) / TW4);
-    const int rounds = (n_tiles + g_num_sms - 1) / g_num_sms;
+    const int rounds = (n_tiles + pl.sms - 1) / pl.sms;
     const int grid = (n_tiles + rounds - 1) / rounds;
     agg_staged_uniform_kernel<TW4, FAN><<<grid, STG_THREADS, pl.smem, st>>>(
         X, ldx, Y, ldy, colidx, wval, src_rows, out_rows, n_rows, n_src, P4, n_tiles, pl.stages);
@@ -520,7 +505,8 @@ extern "C" int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t l
         return DLS_E_ARG;
     if (n_rows == 0 || P == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    int rc = device_props();
+    const DeviceInfo *di = nullptr;
+    int rc = device_info(&di);
     if (rc) return rc;
     const bool vec_ok = aligned16(X) && aligned16(Y) && (ldx % 4 == 0) && (ldy % 4 == 0) &&
                         (((P + 3) / 4) * 4 <= ldx) && (((P + 3) / 4) * 4 <= ldy);
@@ -537,7 +523,7 @@ extern "C" int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t l
     bool can_stage = false;
     const int n_ent = nnz;
     if (n_src_rows > 0 && n_src_rows <= 65535 && nnz >= 0 && (variant == 2 || variant == 3 || variant == 0))
-        can_stage = plan_staged(n_rows, n_src_rows, n_ent, pl) && pl.csr_smem;
+        can_stage = plan_staged(*di, n_rows, n_src_rows, n_ent, pl) && pl.csr_smem;
     if (variant == 3) {
         // the caller asserts a uniform fan-in: rowptr[r] == r * (nnz / n_rows)
         if (!can_stage || nnz % n_rows != 0) return DLS_E_SHAPE;
@@ -556,6 +542,30 @@ extern "C" int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t l
                                                               src_rows, out_rows, n_rows, P4);
     DLS_LAUNCH_CHECK();
     return 0;
+}
+
+// Would `variant` (2 = staged, 3 = staged with uniform fan-in) accept a wave of this shape on the current
+// device?  1 = yes, 0 = no (the gather variant 1 always works), negative = error.  Lets the caller pick a
+// variant up front instead of probing with a launch.
+extern "C" int dls_agg_variant_fits(int32_t variant, int32_t n_rows, int32_t n_src_rows, int32_t nnz)
+{
+    if (n_rows < 0 || n_src_rows < 0 || nnz < 0) return DLS_E_ARG;
+    if (variant == 0 || variant == 1) return 1;
+    if (variant != 2 && variant != 3) return DLS_E_ARG;
+    if (n_rows == 0) return 1;
+    const DeviceInfo *di = nullptr;
+    int rc = device_info(&di);
+    if (rc) return rc < 0 ? rc : -rc;
+    StagedPlan pl;
+    if (n_src_rows <= 0 || n_src_rows > 65535) return 0;
+    if (!(plan_staged(*di, n_rows, n_src_rows, nnz, pl) && pl.csr_smem)) return 0;
+    if (variant == 3) {
+        if (nnz % n_rows != 0) return 0;
+        const int fan = nnz / n_rows;
+        if (fan < 2 || fan > 16) return 0;
+        if ((n_src_rows * pl.tw4 + STG_THREADS - 1) / STG_THREADS > 8) return 0;
+    }
+    return 1;
 }
 
 static int copy_rows_impl(const float *X, int64_t ldx, float *Y, int64_t ldy,

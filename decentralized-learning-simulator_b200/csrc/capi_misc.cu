@@ -1,10 +1,48 @@
 #include "common.cuh"
-namespace dls { int64_t g_launch_count = 0; }
+namespace dls {
+int64_t g_launch_count = 0;
+
+static DeviceInfo g_dev_info[MAX_DEVICES];
+
+int device_info(const DeviceInfo **out, int *dev_out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= MAX_DEVICES) return DLS_E_TOO_BIG;
+    DeviceInfo &di = g_dev_info[dev];
+    if (di.sms == 0) {
+        int sms = 0, smem = 0;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return (int)e;
+        if ((e = cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev)) != cudaSuccess) return (int)e;
+        di.smem_optin = smem;
+        di.sms = sms;
+    }
+    *out = &di;
+    if (dev_out) *dev_out = dev;
+    return 0;
+}
+
+static int g_tune[TUNE_COUNT] = {};
+int tune_value(int key) { return (key >= 0 && key < TUNE_COUNT) ? g_tune[key] : 0; }
+
+int num_sms()
+{
+    const DeviceInfo *di = nullptr;
+    return device_info(&di) == 0 ? di->sms : 0;
+}
+}  // namespace dls
 extern "C" int dls_version(void) { return 100; }
 extern "C" const char *dls_build_info(void) {
     return "dls_b200 sm_100a nvcc " __DATE__ " " __TIME__;
 }
 extern "C" int64_t dls_launch_count(void) { return dls::g_launch_count; }
+extern "C" int dls_tune(int32_t key, int32_t value)
+{
+    if (key < 0 || key >= dls::TUNE_COUNT) return DLS_E_ARG;
+    dls::g_tune[key] = value;
+    return 0;
+}
 
 // ------------------------------------------------------------------------------------------
 // gradient_update wave (dasklearn/functions.py:84-86 -> ModelTrainer.gradient_update,
@@ -43,10 +81,13 @@ extern "C" int dls_gradient_update(float *X, int64_t ldx, const int32_t *p_rows,
                                    const int32_t *out_rows, int32_t n_rows, int64_t P, float lr, float wd,
                                    void *stream)
 {
-    if (!X || !p_rows || !g_rows || !out_rows || n_rows < 0 || P <= 0 || ldx < P || (ldx & 3)) return DLS_E_ARG;
+    if (!X || !p_rows || !g_rows || !out_rows || n_rows < 0 || P <= 0 || ldx < P) return DLS_E_ARG;
+    if (!dls::aligned16(X) || (ldx & 3)) return DLS_E_ALIGN;      // the kernel reads and writes float4
     if (n_rows == 0) return 0;
     const int64_t P4 = (P + 3) / 4;
-    dim3 grid((unsigned)((P4 + 255) / 256 < 148 ? (P4 + 255) / 256 : 148), (unsigned)n_rows);
+    int sms = dls::num_sms();
+    if (sms <= 0) sms = 148;
+    dim3 grid((unsigned)((P4 + 255) / 256 < sms ? (P4 + 255) / 256 : sms), (unsigned)n_rows);
     dls::gradient_update_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ldx, p_rows, g_rows, out_rows, P4, P, lr, wd);
     DLS_LAUNCH_CHECK();
     return 0;

@@ -23,6 +23,35 @@ inline int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
 
 inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// ---- per-device state (a C-ABI caller may drive several GPUs from one process) ----
+constexpr int MAX_DEVICES = 64;
+struct DeviceInfo { int sms = 0; int smem_optin = 0; };
+// Properties of the CURRENT device, queried once per device (capi_misc.cu).
+int device_info(const DeviceInfo **out, int *dev_out = nullptr);
+// Number of SMs of the current device (148 on a B200); 0 if the query fails.
+int num_sms();
+
+// Experiment knobs set through dls_tune() (diagnostic entry point; 0 = automatic choice).
+enum TuneKey { TUNE_AGG_TW4 = 0, TUNE_AGG_STAGES = 1, TUNE_LANES = 2, TUNE_COUNT = 8 };
+int tune_value(int key);
+
+// One-time, per-device opt-in to `bytes` of dynamic shared memory for `kernel`
+// (cudaFuncSetAttribute applies to the device that is current when it is called).
+struct PerDeviceOnce { bool done[MAX_DEVICES] = {}; };
+template <typename K>
+inline int ensure_dyn_smem(K kernel, int bytes, PerDeviceOnce &once) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= MAX_DEVICES) return DLS_E_TOO_BIG;
+    if (!once.done[dev]) {
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e != cudaSuccess) return (int)e;
+        once.done[dev] = true;
+    }
+    return 0;
+}
+
 __device__ __forceinline__ float4 ldg_stream4(const float *p) {
     float4 r;
     asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"

@@ -429,16 +429,19 @@ conv1_wgrad_kernel(Pass p, Ws ws)
 // ------------------------------------------------------------------------------------------
 static int set_attrs()
 {
-    static bool done = false;
-    if (done) return 0;
-    cudaError_t e;
+    static bool done[MAX_DEVICES] = {};                  // per device, like gnlenet.cu
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= MAX_DEVICES) return DLS_E_TOO_BIG;
+    if (done[dev]) return 0;
 #define SET_SMEM(k, bytes) \
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)); if (e != cudaSuccess) return (int)e;
     SET_SMEM((gnl::conv5_kernel<32, 64, 14, true>), 18 * 18 * 32 * 4);
     SET_SMEM((gnl::conv5_kernel<64, 32, 14, false>), 18 * 18 * 64 * 4);
     SET_SMEM((gnl::conv_wgrad_kernel<64, 14>), (18 * 18 * 32 + 196 * 16) * 4);
 #undef SET_SMEM
-    done = true;
+    done[dev] = true;
     return 0;
 }
 

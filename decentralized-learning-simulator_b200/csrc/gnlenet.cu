@@ -635,11 +635,14 @@ gn_param_reduce_kernel(Pass p, Workspace ws)
 // ------------------------------------------------------------------------------------------
 // host-side launch sequences
 // ------------------------------------------------------------------------------------------
-static bool g_attr_done = false;
+static bool g_attr_done[MAX_DEVICES] = {};      // per device: cudaFuncSetAttribute applies to the current device
 static int set_attrs()
 {
-    if (g_attr_done) return 0;
-    cudaError_t e;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= MAX_DEVICES) return DLS_E_TOO_BIG;
+    if (g_attr_done[dev]) return 0;
 #define SET_SMEM(k, bytes)                                                                   \
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)); \
     if (e != cudaSuccess) return (int)e;
@@ -651,7 +654,7 @@ static int set_attrs()
     SET_SMEM((conv_wgrad_kernel<32, 15>), (19 * 19 * 32 + 225 * 16) * 4);
     SET_SMEM((conv_wgrad_kernel<64, 7>), (11 * 11 * 32 + 49 * 16) * 4);
 #undef SET_SMEM
-    g_attr_done = true;
+    g_attr_done[dev] = true;
     return 0;
 }
 
@@ -710,14 +713,14 @@ int classifier(const Pass &p, Workspace &ws, int mode, float *loss_out, float *o
 // stream next to the data-gradient chain (fork/join with events): with one CTA per node, 256 nodes
 // fill 1.73 waves of the 148 SMs, and the other stream's kernels use the SMs an unfinished wave
 // leaves idle.  The side stream is created once per device and joined before this call returns.
-static SideStream g_side[64][2 * MAX_LANES];   // per device: [2*lane] weight-gradient side stream, [2*lane+1] the lane's main stream
+static SideStream g_side[MAX_DEVICES][2 * MAX_LANES];   // per device: [2*lane] weight-gradient side stream, [2*lane+1] the lane's main stream
 
 int side_stream(SideStream **out, int which)
 {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
-    if (dev < 0 || dev >= 64 || which < 0 || which >= 2 * MAX_LANES) return DLS_E_TOO_BIG;
+    if (dev < 0 || dev >= MAX_DEVICES || which < 0 || which >= 2 * MAX_LANES) return DLS_E_TOO_BIG;
     SideStream &ss = g_side[dev][which];
     if (!ss.s) {
         if ((e = cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking)) != cudaSuccess) return (int)e;

@@ -318,16 +318,12 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
                           int bias_off, cudaStream_t st)
 {
     using C = ConvTcCfg<CIN, COUT, H, SB>;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<CIN, COUT, H, SB, BIAS>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
-    // a CTA serves a whole node when there are enough nodes to fill the GPU twice, else half a node
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(conv_tc_kernel<CIN, COUT, H, SB, BIAS>, C::SMEM, attr);
+    if (rc) return rc;
+    // a CTA serves a whole node when there are enough nodes to fill the GPU, else half a node
     int spc = p.gs;
-    if (p.n_groups < 148 && p.gs > SB) spc = ((p.gs / 2 + SB - 1) / SB) * SB;
+    if (p.n_groups < num_sms() && p.gs > SB) spc = ((p.gs / 2 + SB - 1) / SB) * SB;
     const int parts = (p.gs + spc - 1) / spc;
     conv_tc_kernel<CIN, COUT, H, SB, BIAS><<<p.n_groups * parts, CT_THREADS, C::SMEM, st>>>(in, out, p, wprep, wprep_off,
                                                                                    bias_off, spc);
@@ -337,12 +333,9 @@ static int launch_conv_tc(const float *in, float *out, const Pass &p, const __nv
 
 int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st)
 {
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(prep_weights_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PREP_SMEM);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(prep_weights_tc_kernel, PREP_SMEM, attr);
+    if (rc) return rc;
     dim3 grid(6, p.n_models);
     const int32_t *active = p.gmodel ? nullptr : p.gcount;
     prep_weights_tc_kernel<<<grid, 256, PREP_SMEM, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
@@ -581,13 +574,9 @@ static int launch_wgrad_tc(const float *in, const float *dY, const Pass &p, Work
                            cudaStream_t st)
 {
     using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD>;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD>, C::SMEM, attr);
+    if (rc) return rc;
     conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(in, dY, p,
                                                                                                             ws, w_off);
     DLS_LAUNCH_CHECK();

@@ -577,13 +577,9 @@ conv1_wgrad_tc_kernel(Pass p, Workspace ws)
 
 int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             C1W_SMEM);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(conv1_wgrad_tc_kernel, C1W_SMEM, attr);
+    if (rc) return rc;
     conv1_wgrad_tc_kernel<<<p.n_groups, C1W_THREADS, C1W_SMEM, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     return 0;         // conv1's bias gradient: per-sample partials of gn_block_bwd, summed by gn_param_reduce
@@ -599,14 +595,13 @@ int prep_w1_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 
 int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
 {
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(conv1_pool_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1P_SMEM);
-        if (e != cudaSuccess) return (int)e;
-        attr = true;
-    }
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(conv1_pool_tc_kernel, C1P_SMEM, attr);
+    if (rc) return rc;
     const int n_slots = p.n_groups * p.gs;
-    int grid = n_slots < 2 * 148 ? n_slots : 2 * 148;              // two persistent CTAs per SM
+    int sms = num_sms();
+    if (sms <= 0) sms = 148;
+    int grid = n_slots < 2 * sms ? n_slots : 2 * sms;              // two persistent CTAs per SM
     if ((n_slots + grid - 1) / grid > C1P_CAP) grid = (n_slots + C1P_CAP - 1) / C1P_CAP;
     conv1_pool_tc_kernel<<<grid, C1P_THREADS, C1P_SMEM, st>>>(p, ws, save ? 1 : 0);
     DLS_LAUNCH_CHECK();

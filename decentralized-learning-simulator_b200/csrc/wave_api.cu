@@ -1,6 +1,5 @@
 // C-ABI entry points for the train / grad / test waves (see include/dls_b200.h).
 #include "gnlenet.cuh"
-#include <cstdlib>
 
 namespace dls {
 namespace fem {
@@ -99,14 +98,8 @@ static int check_rows(const void *X, int64_t ld, int64_t P)
 // tasks: 11.13 ms per round unsplit, 11.07 ms split 128/128, 10.77 ms split 148/108.
 static int split_point(int n_tasks)
 {
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0, v = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
-            v <= 0)
-            v = 148;
-        sms = v;
-    }
+    int sms = num_sms();                                      // of the current device
+    if (sms <= 0) sms = 148;
     if (n_tasks <= sms) return n_tasks;                       // a single wave: nothing to gain
     int k = (n_tasks + sms) / (2 * sms);                      // round(n / (2 sms))
     if (k < 1) k = 1;
@@ -114,25 +107,12 @@ static int split_point(int n_tasks)
     return na < n_tasks ? na : n_tasks;
 }
 
-// Lanes of a train wave: default two (split_point); DLS_LANES=k (experiments) forces k equal lanes.
+// Lanes of a train wave: two by default (split_point); dls_tune(TUNE_LANES, k) forces k equal lanes (experiments).
 static int lane_split(int n_tasks, int *lane_n, int *lane_off)
 {
-    int k = 0;
-    if (const char *e = getenv("DLS_LANE_SIZES")) {                   // experiments: explicit sizes "148,54,54"
-        int n = 0, off = 0;
-        const char *q = e;
-        while (*q && n < gnl::MAX_LANES && off < n_tasks) {
-            int v = atoi(q);
-            if (v <= 0) break;
-            if (off + v > n_tasks) v = n_tasks - off;
-            lane_n[n] = v; lane_off[n] = off; off += v; ++n;
-            while (*q && *q != ',') ++q;
-            if (*q == ',') ++q;
-        }
-        if (n > 0 && off == n_tasks) return n;
-    }
-    if (const char *e = getenv("DLS_LANES")) k = atoi(e);
-    if (k >= 1 && k <= gnl::MAX_LANES) {
+    const int k0 = tune_value(TUNE_LANES);
+    if (k0 >= 1 && k0 <= gnl::MAX_LANES) {
+        int k = k0;
         if (k > n_tasks) k = n_tasks > 0 ? n_tasks : 1;
         int off = 0;
         for (int h = 0; h < k; ++h) {

@@ -124,8 +124,6 @@ class WaveExecutor:
         copy has run), so the host never waits for kernels queued on the stream — a pageable
         cudaMemcpyAsync would."""
         arrs = [np.ascontiguousarray(a) for a in arrays]
-        if self.device.type != "cuda":
-            return [torch.from_numpy(a.copy()) for a in arrs]
         offs, n = [], 0
         for a in arrs:
             offs.append(n)
@@ -225,19 +223,9 @@ class WaveExecutor:
         if prepared is None:
             prepared = self.prepare_aggregate(model_slots, out_slots, weights)
         rowptr, colidx, wval, src_rows, out_rows, n_src, hint = prepared
-        # auto: shared-memory staged kernels when the wave fits (uniform fan-in -> specialised one),
-        # otherwise the L2 gather kernel.  The first launch of a wave shape settles the choice.
-        order = [variant] if variant else hint["order"]
-        for v in order:
-            try:
-                K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows,
-                           out_rows=out_rows, n_src_rows=n_src, variant=v)
-                if not variant:
-                    hint["order"] = [v]
-                break
-            except DlsError as exc:
-                if "DLS_E_SHAPE" not in str(exc) or v == order[-1]:
-                    raise
+        # auto: the variant the library says fits this wave shape (settled in prepare_aggregate)
+        K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows,
+                   out_rows=out_rows, n_src_rows=n_src, variant=variant or hint["variant"])
         self.stats["agg_rows"] += len(out_slots)
 
     def prepare_aggregate(self, model_slots, out_slots, weights=None):
@@ -261,11 +249,19 @@ class WaveExecutor:
         dev = self.device
         fans = np.diff(rowptr)
         uniform = len(fans) > 0 and int(fans.min()) == int(fans.max()) and 2 <= int(fans[0]) <= 16
-        hint = {"order": ([3] if uniform else []) + [2, 1]}
+        # shared-memory staged kernels when the wave fits (uniform fan-in -> the specialised one), else the
+        # L2 gather kernel: asked of the library (dls_agg_variant_fits), no trial launches
+        hint = {"variant": self._agg_variant(len(out_slots), len(src_index), len(col), uniform)}
         up = self._upload(rowptr, np.asarray(col, dtype=np.int32),
                           np.asarray(w, dtype=np.float64).astype(np.float32), src_rows,
                           np.asarray(out_slots, dtype=np.int32))
         return (*up, len(src_index), hint)
+
+    def _agg_variant(self, n_rows: int, n_src: int, nnz: int, uniform: bool) -> int:
+        for v in ((3, 2) if uniform else (2,)):
+            if K.agg_variant_fits(v, n_rows, n_src, nnz):
+                return v
+        return 1
 
     def test_wave(self, slots: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
         """(accuracy %, mean loss) per slot on the whole test split

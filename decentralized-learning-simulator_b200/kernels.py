@@ -38,6 +38,14 @@ def agg_spmm(X: torch.Tensor, Y: torch.Tensor, rowptr, colidx, wval, P: int, src
     _lib.check(rc, "dls_agg_spmm_f32")
 
 
+def agg_variant_fits(variant: int, n_rows: int, n_src_rows: int, nnz: int) -> bool:
+    """Does aggregate `variant` (2 staged, 3 staged + uniform fan-in) accept this wave shape on the current device?"""
+    rc = _lib.lib().dls_agg_variant_fits(variant, n_rows, n_src_rows, nnz)
+    if rc < 0:
+        _lib.check(rc, "dls_agg_variant_fits")
+    return rc == 1
+
+
 def copy_rows(X, Y, src_rows, dst_rows, P: int):
     _need_cuda(X, Y, src_rows, dst_rows)
     rc = _lib.lib().dls_copy_rows(X.data_ptr(), X.stride(0), Y.data_ptr(), Y.stride(0), _lib.ptr(src_rows),

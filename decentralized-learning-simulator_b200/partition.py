@@ -114,8 +114,16 @@ class DistributedSolver(BatchedSolver):
             for n in names:
                 level_of[n] = li
         remote = {}                               # level -> [(consumer rank, my value consumed there)], one per edge
+        # Levels at which ANY rank has a cut edge: the exchange is a collective over the whole group, so every
+        # rank must enter it at exactly these levels, also when it neither sends nor receives there itself
+        # (irregular graphs: async gossip / AD-PSGD levels, world > 2).
+        xchg_levels = set()
         for name, t in tasks.items():
-            if own[name] != me:
+            mine = own[name]
+            if mine != me:
+                for cons, _ in t["outputs"]:
+                    if own[cons] != mine:
+                        xchg_levels.add(level_of[cons])
                 continue
             for src, _ in t["inputs"]:
                 if own[src] != me and t["func"] != "aggregate":
@@ -126,7 +134,9 @@ class DistributedSolver(BatchedSolver):
                     if tasks[cons]["func"] != "aggregate":
                         raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % cons)
                     remote.setdefault(level_of[cons], []).append((q, (name, idx)))
+                    xchg_levels.add(level_of[cons])
         self._remote = remote
+        self._xchg_levels = xchg_levels
         # the base planner only looks at this rank's tasks
         return [[n for n in names if own[n] == me] for names in levels]
 
@@ -159,7 +169,7 @@ class DistributedSolver(BatchedSolver):
                 self._halo_of[m] = h
                 h += 1
         n_send = sum(len(x) for x in send_l)
-        if h or n_send:
+        if h or n_send or level in self._xchg_levels:
             self._level_xchg[level] = {"send_slots": [self._value_slot[m] for x in send_l for m in x],
                                        "send_counts": [len(x) for x in send_l],
                                        "recv_counts": [len(x) for x in recv_l]}

@@ -43,6 +43,10 @@ int         dls_version(void);
 const char *dls_build_info(void);
 /* Number of kernels this library has launched in the calling process (all entry points). */
 int64_t     dls_launch_count(void);
+/* Diagnostic knobs for experiments (scripts/): key 0 = aggregate tile width in float4 columns, 1 = aggregate
+ * pipeline stages, 2 = number of equal lanes a train wave is split into; value 0 restores the automatic
+ * choice.  Process-wide, not thread-safe, never needed for correct results.  No reference counterpart. */
+int         dls_tune(int32_t key, int32_t value);
 
 /* ------------------------------------------------------------------------------------------
  * aggregate wave — replaces N calls of functions.aggregate -> ModelManager ->
@@ -65,6 +69,9 @@ int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t ldy,
                      const int32_t *rowptr, const int32_t *colidx, const float *wval,
                      const int32_t *src_rows, const int32_t *out_rows, int32_t n_rows,
                      int32_t n_src_rows, int32_t nnz, int64_t P, int32_t variant, void *stream);
+/* 1 if `variant` (2 or 3) accepts a wave of this shape on the current device, 0 if not (variant 1 always
+ * does), negative on bad arguments: lets the caller choose a variant without a trial launch. */
+int dls_agg_variant_fits(int32_t variant, int32_t n_rows, int32_t n_src_rows, int32_t nnz);
 
 /* Row plumbing on the stacked tensor (replaces the pickle round-trip copies of
  * serialize_model/unserialize_model, dasklearn/models/__init__.py:9-16). */
@@ -114,7 +121,8 @@ int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G, int64_t l
  * with a supplied gradient, X[out_rows[r]] = X[p_rows[r]] - lr * (X[g_rows[r]] + wd * X[p_rows[r]])
  * (single rounding, like torch's add_(buf, alpha=-lr)); gradients live in rows of X (as written by
  * dls_grad_wave followed by dls_copy_rows).  out_rows[r] may equal p_rows[r] (in place); rows of
- * different r must not alias.  The node's momentum rows are not touched. */
+ * different r must not alias.  The node's momentum rows are not touched.  X must be 16-byte aligned and
+ * ldx a multiple of 4 (DLS_E_ALIGN otherwise): the kernel moves float4. */
 int dls_gradient_update(float *X, int64_t ldx, const int32_t *p_rows, const int32_t *g_rows,
                         const int32_t *out_rows, int32_t n_rows, int64_t P, float lr, float wd, void *stream);
 
@@ -124,7 +132,8 @@ int dls_gradient_update(float *X, int64_t ldx, const int32_t *p_rows, const int3
  *
  * Evaluates `n_models` rows on the same `n_test` images.  Outputs per model:
  *   out_correct[m]   number of argmax hits (first maximum wins, like torch.argmax)
- *   out_loss_sum[m]  sum over samples of the per-sample loss (fp64 accumulation of fp32 terms)
+ *   out_loss_sum[m]  sum over samples of the per-sample loss (fp32 within each group of 32 samples,
+ *                    fp64 across the groups, in sample order)
  * The caller derives accuracy = correct / n_test * 100 and loss = loss_sum / n_test.
  * ------------------------------------------------------------------------------------------ */
 int64_t dls_eval_workspace_bytes(int32_t arch, int32_t n_models, int32_t n_test);
@@ -149,7 +158,8 @@ int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, in
  * forwards model / image / result buffers, a monitoring thread while the solver owns the training
  * workspace, a caller that must avoid cudaMalloc's device-wide synchronisation mid-round).
  *
- * Same outputs as dls_eval_wave (fp32 path, no logits).  The scratch memory is a fixed 32 MiB
+ * GNLeNet only (arch must be DLS_ARCH_GNLENET; DLS_E_SHAPE for the FEMNIST CNN, whose fc1 activations
+ * do not fit the fixed scratch).  Same outputs as dls_eval_wave (fp32 path, no logits).  The scratch memory is a fixed 32 MiB
  * array inside the library, present on every GPU that loads it until the process exits; it
  * limits a call to n_models <= 16 and n_test <= 4096, beyond which DLS_E_TOO_BIG is returned.
  * The call itself performs no allocation of any kind.  All calls on a device share that array

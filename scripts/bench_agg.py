@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 import dls_b200  # noqa: F401
-from dls_b200 import kernels as K, synthetic
+from dls_b200 import _lib, kernels as K, synthetic
 from dls_b200.layout import GNLENET as L
 
 
@@ -48,11 +48,8 @@ def main():
         if args.sweep:
             configs = [(1, None, None)] + [(v, tw, st) for v in (2, 3) for tw in (4, 8, 16) for st in (2, 3, 4)]
         for v, tw, stg in configs:
-            for key, val in (("DLS_AGG_TW4", tw), ("DLS_AGG_STAGES", stg)):
-                if val is None:
-                    os.environ.pop(key, None)
-                else:
-                    os.environ[key] = str(val)
+            _lib.lib().dls_tune(0, int(tw or 0))            # aggregate tile width (0 = auto)
+            _lib.lib().dls_tune(1, int(stg or 0))           # aggregate pipeline stages (0 = auto)
             try:
                 times = []
                 for it in range(args.iters + 3):

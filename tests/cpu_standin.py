@@ -30,6 +30,13 @@ class OracleExecutor(WaveExecutor):
         self.init_row = torch.from_numpy(O.initial_row(self.layout, settings.seed))
         self.stats = {"train_tasks": 0, "train_steps": 0, "agg_rows": 0, "test_tasks": 0}
 
+    def _upload(self, *arrays):
+        """CPU stand-in of WaveExecutor._upload (the product one stages through pinned memory to a CUDA device)."""
+        return [torch.from_numpy(np.ascontiguousarray(a).copy()) for a in arrays]
+
+    def _agg_variant(self, n_rows, n_src, nnz, uniform):
+        return 1
+
     def init_rows(self, slots):
         for s in slots:
             self.X[s] = self.init_row

@@ -89,6 +89,64 @@ def test_two_ranks_equal_single_process_oracle(tmp_path, how):
     assert halo[0][0] + halo[1][0] > 0
 
 
+def _gossip_worker(rank, world, port, tmp, owner, n, events, out_q):
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from cpu_standin import OracleExecutor
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    dag = synthetic.gossip_dag(n, events, seed=3)
+    imgs, labs = synthetic.make_partitions(n, N_I, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(N_TEST, 32, 3, 10)
+    owned = [int(p) for p in np.nonzero(np.asarray(owner) == rank)[0]]
+    st = SessionSettings(participants=n, seed=42, data_dir=tmp, learning=LearningSettings(0.002, 0.9, 0.0, 32, STEPS))
+    ex = OracleExecutor(st, imgs, labs, timg, tlab, owned, N_I)
+    solver = DistributedSolver(ex, dag, rank, world, owner)
+    res = solver.run()                       # streamed: one level at a time, every rank in every exchange
+    out = {name: h[0].executor.X[h[0].slot, :L.P].numpy().copy() for name, h in res.items()}
+    n_xchg = sum(1 for w in solver.waves if getattr(w, "xchg", None))
+    idle = sum(1 for w in solver.waves if getattr(w, "xchg", None)
+               and sum(w.xchg["send_counts"]) + sum(w.xchg["recv_counts"]) == 0)
+    out_q.put((rank, out, n_xchg, idle))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_three_ranks_irregular_gossip_graph(tmp_path):
+    """World size 3 on an asynchronous gossip graph: at most levels only SOME ranks have a cut edge.  The
+    exchange is a collective, so every rank must enter it at every level where any rank exchanges (a rank
+    that skipped it would hang or desynchronise the group); results must equal the sequential oracle."""
+    from oracle import oracle as O
+    torch.set_num_threads(1)
+    n, events, world = 6, 9, 3
+    dag = synthetic.gossip_dag(n, events, seed=3)
+    owner = block_partition(n, world)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gossip_worker, args=(r, world, port, str(tmp_path), owner.tolist(), n, events, q))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    got, n_xchg, idle = {}, [], 0
+    for _ in range(world):
+        rank, out, nx, nidle = q.get(timeout=300)
+        got.update(out)
+        n_xchg.append(nx)
+        idle += nidle
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert len(set(n_xchg)) == 1 and n_xchg[0] > 0      # the same number of collectives on every rank
+    assert idle > 0                                      # and some rank took part without rows of its own
+    imgs, labs = synthetic.make_partitions(n, N_I, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(N_TEST, 32, 3, 10)
+    sinks, _ = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=42, batch=32, local_steps=STEPS, lr=0.002, mu=0.9,
+                           wd=0.0, n_i=N_I, minibatch_permutation=synthetic.minibatch_permutation)
+    assert sorted(got) == sorted(sinks)
+    for name, row in sinks.items():
+        assert np.array_equal(got[name], row[:L.P]), name
+
+
 def test_partition_ring_has_two_cut_edges_per_rank():
     """The reference's ring relabels nodes randomly (dpsgd/simulation.py:37-41); the BFS partition
     recovers contiguity: each rank needs exactly 2 remote rows."""

@@ -62,6 +62,17 @@ def test_noalloc_matches_eval_wave_twice_in_a_row(cuda):
         assert torch.equal(correct, want_correct), (correct, want_correct)
         np.testing.assert_allclose(loss.cpu().numpy(), want_loss.cpu().numpy(), rtol=1e-12)
         assert int(want_correct.sum()) > 0 and bool(torch.isfinite(want_loss).all())
+    # torch's counter above only sees torch's caching allocator.  A cudaMalloc made inside the library would
+    # show up as less free device memory instead, so repeat the (now warm: every kernel is loaded) last call
+    # and require that the device's free byte count did not drop.
+    correct.fill_(-7)
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info(cuda)[0]
+    rc = _call_noalloc(X, rows, timg, tlab, correct, loss)
+    assert rc == 0, _lib.ERRORS.get(rc, rc)
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info(cuda)[0] >= free_before, "dls_eval_wave_noalloc allocated device memory"
+    assert torch.equal(correct, want_correct)
 
 
 def test_noalloc_rejects_oversize_and_bad_arguments(cuda):

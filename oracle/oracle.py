@@ -8,8 +8,12 @@ Parity pin: `tests/test_oracle_golden.py` checks every function here against fix
 `tests/golden/` that were produced by running the UNMODIFIED reference package from
 `/root/reference` (see `tests/golden/make_golden.py`).  The reference's own tests hold no
 numerical vectors for this path, so reference-generated fixtures are the pin.
-FEMNIST cannot be run by the reference at all (`dasklearn/models/femnist.py:5` imports a missing
-module): for FEMNIST this file is a restatement with **parity unpinned**.
+FEMNIST: the reference's trainer / evaluator refuse the dataset (`model_trainer.py:77-78`,
+`model_evaluator.py:36-37`) and its model file imports a module that is not in the tree
+(`dasklearn/models/femnist.py:5`).  With that module supplied as a two-constant shim the reference's own
+`CNN` class runs, and `tests/golden/femnist_kat.npz` (init, logits, loss, autograd gradients, three
+optimizer steps — all produced by the reference's model + optimizer classes) pins the FEMNIST functions
+here; only the evaluation loop for FEMNIST (argmax accuracy + CE sum) remains a restatement without a pin.
 """
 import ctypes
 import os
@@ -318,6 +322,88 @@ def initial_row(layout, seed: int) -> np.ndarray:
 
 
 # ---------------------------------------------------------------------------------------------
+# chunk / reconstruct_from_chunks — dasklearn/functions.py:136-146 -> ChunkManager
+# (dasklearn/simulation/conflux/chunk_manager.py:12-53)
+# ---------------------------------------------------------------------------------------------
+
+def chunk_bounds(P: int, n: int) -> List[Tuple[int, int]]:
+    """Column ranges of ChunkManager.chunk_model (chunk_manager.py:13-25): n slices of P // n elements of the
+    flat state_dict (== parameters() order for these buffer-free models); the last takes the remainder."""
+    size = P // n
+    b = [(i * size, (i + 1) * size) for i in range(n)]
+    b[-1] = (b[-1][0], P)
+    return b
+
+
+def _cascade_sum(rows: np.ndarray) -> np.ndarray:
+    """torch's CPU `multi_row_sum` (aten/src/ATen/native/cpu/SumKernel.cpp, torch 2.x) over axis 0: sequential
+    accumulation from 0 with a 4-level cascade every 16 rows (level_step = max(16, ...))."""
+    size = rows.shape[0]
+    num_levels = 4
+    level_power = max(4, (int(np.ceil(np.log2(size))) if size > 1 else 0) // num_levels)
+    level_step = 1 << level_power
+    level_mask = level_step - 1
+    acc = [np.zeros(rows.shape[1], np.float32) for _ in range(num_levels)]
+    i = 0
+    while i + level_step <= size:
+        for _ in range(level_step):
+            acc[0] = acc[0] + rows[i]
+            i += 1
+        for j in range(1, num_levels):
+            acc[j] = acc[j] + acc[j - 1]
+            acc[j - 1] = np.zeros_like(acc[0])
+            if (i & (level_mask << (j * level_power))) != 0:
+                break
+    while i < size:
+        acc[0] = acc[0] + rows[i]
+        i += 1
+    for j in range(1, num_levels):
+        acc[0] = acc[0] + acc[j]
+    return acc[0]
+
+
+def _ilp4_sum(rows: np.ndarray) -> np.ndarray:
+    """torch's CPU `row_sum`: four interleaved partial sums (rows 4i+q), remainder rows into partial 0,
+    then p0 + p1 + p2 + p3."""
+    size = rows.shape[0]
+    g = size // 4
+    parts = [_cascade_sum(rows[q:4 * g:4]) if g else np.zeros(rows.shape[1], np.float32) for q in range(4)]
+    for i in range(4 * g, size):
+        parts[0] = parts[0] + rows[i]
+    return ((parts[0] + parts[1]) + parts[2]) + parts[3]
+
+
+def mean_stack(pieces: Sequence[np.ndarray]) -> np.ndarray:
+    """`torch.mean(torch.stack(pieces), dim=0)` for fp32 pieces of equal length n, bit for bit as torch's CPU
+    kernel (AVX2 dispatch, vector width 8) evaluates it — chunk_manager.py:40.  The reduction runs over the
+    outer dimension of the contiguous [k, n] stack (`vectorized_outer_sum`): columns below the last multiple
+    of 32 are summed sequentially over the contributors (with the 16-row cascade); the remaining columns go
+    through `row_sum`, four interleaved partial sums.  The sum is then DIVIDED by k (sum(...).div_(k))."""
+    rows = np.stack([np.asarray(p, dtype=np.float32) for p in pieces])
+    k, n = rows.shape
+    out = np.empty(n, np.float32)
+    if n >= 8:
+        nb = (n // 32) * 32
+    else:
+        nb = (n // 4) * 4                 # scalar_outer_sum: groups of four columns, then row_sum
+    if nb:
+        out[:nb] = _cascade_sum(rows[:, :nb])
+    if nb < n:
+        out[nb:] = _ilp4_sum(rows[:, nb:])
+    return out / np.float32(k)
+
+
+def reconstruct_from_chunks(P: int, chunks: Sequence[Sequence[np.ndarray]]) -> np.ndarray:
+    """ChunkManager.reconstruct_model (chunk_manager.py:34-53): per chunk index the mean over the received
+    pieces (in arrival order), concatenated back into the flat model."""
+    for idx, c in enumerate(chunks):
+        assert len(c), "No chunks received at index %d!" % idx            # chunk_manager.py:36
+    flat = np.concatenate([mean_stack(c) for c in chunks])
+    assert flat.size == P
+    return flat
+
+
+# ---------------------------------------------------------------------------------------------
 # sequential compute-graph solve — Worker.start dasklearn/worker.py:21-38 and
 # Broker.handle_task_result dasklearn/broker.py:277-290 ("1 broker / 1 worker")
 # ---------------------------------------------------------------------------------------------
@@ -387,11 +473,20 @@ def solve_dag(layout, serialized_tasks, part_images, part_labels, test_images, t
             grads[(name, 0)] = gfull
         elif t["func"] == "gradient_update":                        # functions.py:84-86
             res = gradient_update_task(values[_ref(d["model"])], grads[_ref(d["gradient_model"])], layout.P, lr, wd)
+        elif t["func"] == "chunk":                                  # functions.py:136-140
+            res = values[_ref(d["model"])]
+            for ci, (c0, c1) in enumerate(chunk_bounds(layout.P, int(d["n"]))):
+                values[(name, ci)] = res[c0:c1]
+        elif t["func"] == "reconstruct_from_chunks":                # functions.py:142-146
+            flat_ = reconstruct_from_chunks(layout.P, [[values[tuple(m)] for m in c] for c in d["chunks"]])
+            res = np.zeros(layout.ld, dtype=np.float32)
+            res[:layout.P] = flat_
         else:
             raise RuntimeError("Task function %s not found!" % t["func"])     # worker.py:26-27
         if timings is not None:
             timings.setdefault(t["func"], []).append(_time.perf_counter() - t0)
-        values[(name, 0)] = res
+        if t["func"] != "chunk":
+            values[(name, 0)] = res
         if not t["outputs"]:
             sinks[name] = res
         for nxt, idx_ in t["outputs"]:

@@ -11,6 +11,13 @@ modified or copied.  Fixtures:
   train_kat.npz    functions.train for one peer, two consecutive rounds (momentum carry-over,
                    partial last batch: n_i=80 -> steps of 32, 32, 16)
   dpsgd_mini.*     full DES -> DAG -> sequential solve: 8 nodes, 2-regular, 3 rounds, test at round 3
+  dpsgd_c1.*       BASELINE config C1 solved by the reference: 16 nodes, 4-regular, 5 rounds of 5 local
+                   steps (n_i = 320), test at round 5
+  femnist_kat.npz  the reference's own FEMNIST `CNN` class (dasklearn/models/femnist.py:45-85, importable
+                   once the missing module `dasklearn.datasets.femnist` is supplied as a two-constant shim):
+                   init under manual_seed(42), logits, CrossEntropy loss, autograd gradients and three
+                   steps of the reference's SGDOptimizer (lr 0.004, momentum 0) on scripted minibatches
+  chunk_kat.npz    functions.chunk / functions.reconstruct_from_chunks on GNLeNet models (1..9 contributors)
 """
 import asyncio
 import hashlib
@@ -299,6 +306,128 @@ def gen_dpsgd_mini(work_dir):
     print(acc_rows[0])
 
 
+def gen_c1(work_dir):
+    """BASELINE config C1 (37 s on CPU): D-PSGD, 16 nodes, 4-regular, 5 rounds, test at 5."""
+    n, k, rounds, n_i, steps, n_test = 16, 4, 5, 320, 5, 256
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(n_test, 32, 3, 10)
+    ds = SyntheticFederatedDataset(imgs, labs, timg, tlab)
+    reset_reference_globals(ds)
+    settings = make_settings(n, rounds, k, work_dir, local_steps=steps, test_interval=rounds)
+    sim = run_des(settings)
+    serialized = sim.workflow_dag.serialize()
+    os.makedirs(settings.data_dir, exist_ok=True)
+    sinks = solve_sequential(serialized, settings, ds, n_i)
+    final = np.zeros((n, GNLENET.P), dtype=np.float32)
+    for name, res in sinks.items():
+        peer = int(name.split("_")[1])
+        final[peer] = flat(res[0])
+    acc_rows = []
+    for peer in range(n):
+        with open(os.path.join(settings.data_dir, "accuracies_%d.csv" % peer)) as f:
+            acc_rows.append(f.read())
+    with open(os.path.join(HERE, "dpsgd_c1_dag.pkl"), "wb") as f:
+        pickle.dump(serialized, f, protocol=4)
+    np.savez_compressed(os.path.join(HERE, "dpsgd_c1.npz"),
+                        final_node0=final[0], final_node11=final[11],
+                        final_sum=final.astype(np.float64).sum(axis=1),
+                        final_l2=np.sqrt((final.astype(np.float64) ** 2).sum(axis=1)),
+                        final_strided=final[:, ::16].copy(),
+                        acc_csv=np.array(acc_rows),
+                        meta=np.array(json.dumps({"n": n, "k": k, "rounds": rounds, "n_i": n_i, "local_steps": steps,
+                                                  "n_test": n_test, "seed": SEED, "batch": 32, "lr": 0.002,
+                                                  "momentum": 0.9, "wd": 0.0, "torch": torch.__version__,
+                                                  "threads": 1, "n_tasks": len(serialized)})))
+    print("dpsgd_c1 written: %d tasks" % len(serialized))
+    print(acc_rows[0])
+
+
+def gen_femnist():
+    """Pin the FEMNIST CNN to the reference's OWN model class.  dasklearn/models/femnist.py:5 imports
+    `dasklearn.datasets.femnist`, a module that is not in the reference tree; supplying it as a shim with the
+    two constants it is asked for makes `create_model("femnist")` work unmodified.  The
+    reference's trainer refuses the dataset (model_trainer.py:77-78), so the loop around the model is
+    model_trainer.py:99-126 driven by hand: CrossEntropyLoss (:117-118) + the reference's SGDOptimizer."""
+    import types
+    from dls_b200.layout import FEMNIST
+    shim = types.ModuleType("dasklearn.datasets.femnist")
+    shim.FLAT_SIZE, shim.NUM_CLASSES = 28 * 28, 62
+    sys.modules["dasklearn.datasets.femnist"] = shim
+    from dasklearn.optimizer.sgd import SGDOptimizer
+    torch.manual_seed(SEED)
+    m = create_model("femnist")
+    assert type(m).__module__ == "dasklearn.models.femnist" and type(m).__name__ == "CNN"
+    init = flat(m)
+    assert init.size == FEMNIST.P
+    n_i, B = 96, 32
+    imgs, labs = synthetic.make_images(n_i, 28, 1, 62, seed=1234 + 7)
+    order = synthetic.minibatch_permutation(SEED, 7, 1, n_i)
+    x_all = torch.from_numpy(imgs).permute(0, 3, 1, 2).contiguous().to(torch.float32) / 255.0   # ToTensor
+    y_all = torch.from_numpy(labs.astype(np.int64))
+    sel = order[:B]
+    out = m(x_all[sel])
+    loss = torch.nn.CrossEntropyLoss()(out, y_all[sel])
+    m.zero_grad()
+    loss.backward()
+    grad = torch.cat([p.grad.reshape(-1) for p in m.parameters()]).numpy().astype(np.float32)
+    # three optimizer steps (lr 0.004, momentum 0: args.py:70-72), last batch partial (96 = 32 + 32 + 32 -> use 32,32,20)
+    opt = SGDOptimizer(m, 0.004, 0.0, 0.0)
+    counts = [32, 32, 20]
+    losses = []
+    for s, c in enumerate(counts):
+        b = order[s * B: s * B + c]
+        m.train()
+        opt.optimizer.zero_grad()
+        l = torch.nn.CrossEntropyLoss()(m.forward(x_all[b]), y_all[b])
+        l.backward()
+        opt.optimizer.step()
+        losses.append(float(l.detach()))
+    after = flat(m)
+    with torch.no_grad():
+        logits_after = m(x_all[order[:64]]).numpy()
+    ent = {e[0]: (e[2], int(np.prod(e[1]))) for e in FEMNIST.entries}
+    o1, n1 = ent["fc1.weight"]
+    keep = np.ones(FEMNIST.P, dtype=bool)
+    keep[o1:o1 + n1] = False
+    keep[o1:o1 + n1:16] = True                                   # fc1.weight (1.6 M values) is kept 1 in 16
+    np.savez_compressed(os.path.join(HERE, "femnist_kat.npz"),
+                        init_sha=np.frombuffer(bytes.fromhex(sha(init)), dtype=np.uint8),
+                        init_strided=init[::64].copy(), logits=out.detach().numpy(), loss=np.float32(loss.item()),
+                        grad_kept=grad[keep], grad_l2=np.float64(np.linalg.norm(grad.astype(np.float64))),
+                        after_kept=after[keep], after_sum=np.float64(after.astype(np.float64).sum()),
+                        step_losses=np.array(losses, dtype=np.float64), logits_after=logits_after,
+                        meta=np.array(json.dumps({"n_i": n_i, "batch": B, "peer": 7, "round": 1, "seed": SEED,
+                                                  "counts": counts, "lr": 0.004, "momentum": 0.0, "wd": 0.0,
+                                                  "image_seed": 1234 + 7, "fc1_stride": 16,
+                                                  "torch": torch.__version__, "threads": 1})))
+    print("femnist_kat.npz written; loss %.6f, |g| %.6f" % (loss.item(), np.linalg.norm(grad)))
+
+
+def gen_chunks(work_dir):
+    """Shatter/Conflux chunk ops (functions.py:136-146 -> ChunkManager, simulation/conflux/chunk_manager.py:12-53):
+    `chunk` slices the flat state_dict into n pieces (the last takes the remainder); `reconstruct_from_chunks`
+    averages, per chunk index, the pieces of a VARIABLE set of contributors with torch.mean(torch.stack(..), 0)."""
+    settings = make_settings(16, 1, 4, work_dir)
+    n_chunks = 6
+    contributors = [1, 2, 3, 4, 5, 9]                 # contributor count per chunk index
+    n_models = max(contributors)
+    X = kat_rows(n_models, GNLENET.P, salt=777)
+    models = [model_from_flat(X[i]) for i in range(n_models)]
+    pieces = [RF.chunk(settings, {"model": mm, "n": n_chunks}) for mm in models]
+    sizes = [int(c.numel()) for c in pieces[0]]
+    # contributor sets: chunk c is averaged over models (c, c+1, ...) mod n_models, in that order
+    sets = [[(c + j) % n_models for j in range(contributors[c])] for c in range(n_chunks)]
+    chunks = [[pieces[mi][c] for mi in sets[c]] for c in range(n_chunks)]
+    res = RF.reconstruct_from_chunks(settings, {"chunks": chunks})
+    assert isinstance(res, list) and len(res) == 1
+    np.savez_compressed(os.path.join(HERE, "chunk_kat.npz"), y=flat(res[0]), sizes=np.array(sizes, dtype=np.int64),
+                        sets=np.array(json.dumps(sets)), in_sha=np.frombuffer(bytes.fromhex(sha(X)), dtype=np.uint8),
+                        piece0_of_model1=pieces[1][0].numpy().copy(),
+                        meta=np.array(json.dumps({"n_chunks": n_chunks, "n_models": n_models, "salt": 777,
+                                                  "torch": torch.__version__, "threads": 1})))
+    print("chunk_kat.npz written; chunk sizes", sizes)
+
+
 def gen_c2_dag(work_dir):
     """The reference DES's own compute graph for BASELINE config C2 (256 nodes, k = log2 N = 8),
     2 rounds, so the bench can replay a real coordinator-produced DAG."""
@@ -314,8 +443,11 @@ def gen_c2_dag(work_dir):
 if __name__ == "__main__":
     import tempfile
     wd = tempfile.mkdtemp(prefix="golden_")
-    if len(sys.argv) > 1 and sys.argv[1] == "gradient":          # only the AD-PSGD known-answer file
-        gen_gradient(wd)
+    if len(sys.argv) > 1:                                         # only the named fixtures
+        for what in sys.argv[1:]:
+            {"gradient": lambda: gen_gradient(wd), "c1": lambda: gen_c1(wd), "femnist": gen_femnist,
+             "chunks": lambda: gen_chunks(wd), "fedavg": lambda: gen_fedavg(wd), "train": lambda: gen_train(wd),
+             "mini": lambda: gen_dpsgd_mini(wd), "c2dag": lambda: gen_c2_dag(wd), "init": gen_init}[what]()
         sys.exit(0)
     gen_fedavg(wd)
     gen_init()
@@ -323,3 +455,6 @@ if __name__ == "__main__":
     gen_gradient(wd)
     gen_dpsgd_mini(wd)
     gen_c2_dag(wd)
+    gen_c1(wd)
+    gen_femnist()
+    gen_chunks(wd)

@@ -126,3 +126,110 @@ def test_compute_gradient_and_gradient_update_known_answers(golden_dir):
     perm3 = synthetic.minibatch_permutation(meta["seed"], peer, 3, meta["n_i"])[:32]
     g2, _ = O.gradient_of(L, t["upd2"], imgs[peer][perm3], labs[peer][perm3])
     check(g2, t["grad2"])
+
+
+def test_dpsgd_c1_full_solve(golden_dir):
+    """BASELINE config C1 (16 nodes, 4-regular, 5 rounds x 5 local steps, test at round 5) as solved by the
+    reference itself (make_golden.py gen_c1): the oracle reproduces every node's final model and CSV row."""
+    g = np.load(os.path.join(golden_dir, "dpsgd_c1.npz"))
+    meta = json.loads(str(g["meta"]))
+    with open(os.path.join(golden_dir, "dpsgd_c1_dag.pkl"), "rb") as f:
+        dag = pickle.load(f)
+    n = meta["n"]
+    assert (n, meta["k"], meta["rounds"]) == (16, 4, 5)
+    assert len(dag) == meta["n_tasks"] == 2 * meta["rounds"] * n + n
+    assert all(len(t["data"]["models"]) == meta["k"] + 1 for t in dag if t["func"] == "aggregate")
+    imgs, labs = synthetic.make_partitions(n, meta["n_i"], 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(meta["n_test"], 32, 3, 10)
+    sinks, acc = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=meta["seed"], batch=32,
+                             local_steps=meta["local_steps"], lr=0.002, mu=0.9, wd=0.0, n_i=meta["n_i"],
+                             minibatch_permutation=synthetic.minibatch_permutation)
+    final = np.zeros((n, L.P), np.float32)
+    for name, row in sinks.items():
+        final[int(name.split("_")[1])] = row[:L.P]
+    if torch.__version__ == meta["torch"]:
+        assert np.array_equal(final[0], g["final_node0"])
+        assert np.array_equal(final[11], g["final_node11"])
+        assert np.array_equal(final[:, ::16], g["final_strided"])
+    else:
+        np.testing.assert_allclose(final[:, ::16], g["final_strided"], rtol=1e-5, atol=1e-7)
+    for peer, rnd, t_us, a, l in acc:
+        line = "dpsgd,cifar10,iid,%g,%d,%d,%.2f,%f,%f" % (1, peer, rnd, t_us / 1e6, a, l)
+        assert line in str(g["acc_csv"][peer])
+
+
+def femnist_kept_mask(LF, stride):
+    o1 = LF.offset("fc1.weight")
+    n1 = 512 * 3136
+    keep = np.ones(LF.P, dtype=bool)
+    keep[o1:o1 + n1] = False
+    keep[o1:o1 + n1:stride] = True
+    return keep
+
+
+def test_femnist_pinned_to_reference_model_class(golden_dir):
+    """FEMNIST CNN: init, logits, CrossEntropy loss, autograd gradients and three SGD steps (32, 32, 20
+    samples) produced by the reference's own `CNN` + `SGDOptimizer` classes (make_golden.py gen_femnist)."""
+    import hashlib
+    from dls_b200.layout import FEMNIST as LF
+    from dls_b200.models import initial_row
+    g = np.load(os.path.join(golden_dir, "femnist_kat.npz"))
+    meta = json.loads(str(g["meta"]))
+    exact = torch.__version__ == meta["torch"]
+    init = O.initial_row(LF, meta["seed"])
+    assert hashlib.sha256(init[:LF.P].tobytes()).digest() == bytes(g["init_sha"])
+    assert np.array_equal(initial_row(LF, meta["seed"]).numpy(), init)           # product-side init, same bits
+    assert np.array_equal(init[:LF.P:64], g["init_strided"])
+    imgs, labs = synthetic.make_images(meta["n_i"], 28, 1, 62, seed=meta["image_seed"])
+    order = synthetic.minibatch_permutation(meta["seed"], meta["peer"], meta["round"], meta["n_i"])
+    B = meta["batch"]
+    sel = order[:B]
+    keep = femnist_kept_mask(LF, meta["fc1_stride"])
+
+    def check(a, b, tol=1e-5):
+        if exact:
+            assert np.array_equal(a, b)
+        else:
+            np.testing.assert_allclose(a, b, rtol=tol, atol=1e-7)
+
+    check(O.logits(LF, init, imgs[sel]), g["logits"])
+    grad, loss = O.gradient_of(LF, init, imgs[sel], labs[sel])
+    check(np.float32(loss), g["loss"])
+    check(grad[keep], g["grad_kept"])
+    idx = -np.ones((3, B), np.int32)
+    cnt = np.array(meta["counts"], np.int32)
+    for s, c in enumerate(cnt):
+        idx[s, :c] = order[s * B: s * B + c]
+    row, mom, losses = O.train_task(LF, init, None, imgs, labs, idx, cnt, meta["lr"], meta["momentum"], meta["wd"])
+    assert mom is None
+    check(row[:LF.P][keep], g["after_kept"])
+    np.testing.assert_allclose(losses, g["step_losses"], rtol=1e-6)
+    check(O.logits(LF, row, imgs[order[:64]]), g["logits_after"])
+
+
+def test_chunk_ops_known_answers(golden_dir):
+    """functions.chunk / reconstruct_from_chunks of the reference (make_golden.py gen_chunks): the slice
+    bounds and torch.mean(torch.stack(...), 0)'s summation order for 1..9 contributors, bit for bit."""
+    g = np.load(os.path.join(golden_dir, "chunk_kat.npz"))
+    meta = json.loads(str(g["meta"]))
+    sets = json.loads(str(g["sets"]))
+    X = kat_rows(meta["n_models"], L.P, salt=meta["salt"])
+    bounds = O.chunk_bounds(L.P, meta["n_chunks"])
+    assert [c1 - c0 for c0, c1 in bounds] == list(g["sizes"])
+    assert np.array_equal(X[1][bounds[0][0]:bounds[0][1]], g["piece0_of_model1"])
+    y = O.reconstruct_from_chunks(L.P, [[X[mi][c0:c1] for mi in sets[c]] for c, (c0, c1) in enumerate(bounds)])
+    assert np.array_equal(y.view(np.uint32), g["y"].view(np.uint32))
+    # the fixture separates torch's order from a plain sequential mean (tail columns of chunks with >= 5 pieces)
+    c0, c1 = bounds[4]
+    seq = np.zeros(c1 - c0, np.float32)
+    for mi in sets[4]:
+        seq = seq + X[mi][c0:c1]
+    assert not np.array_equal(seq / np.float32(len(sets[4])), g["y"][c0:c1])
+
+
+@pytest.mark.parametrize("n,k", [(2, 3), (7, 9), (33, 5), (100, 18), (257, 40)])
+def test_mean_stack_matches_torch(n, k):
+    rs = np.random.RandomState(n * 1000 + k)
+    x = (rs.standard_normal((k, n)) * np.exp2(rs.randint(-8, 8, (k, n)))).astype(np.float32)
+    y = torch.mean(torch.stack([torch.from_numpy(x[i].copy()) for i in range(k)]), dim=0).numpy()
+    assert np.array_equal(y.view(np.uint32), O.mean_stack(list(x)).view(np.uint32))

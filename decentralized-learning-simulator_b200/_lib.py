@@ -25,6 +25,8 @@ SIGNATURES = {
     "dls_agg_variant_fits": (c_int, [c_int32, c_int32, c_int32, c_int32]),
     "dls_agg_spmm_f32": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int64, c_int32, c_void_p]),
+    "dls_chunk_mean_f32": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_int32, c_int32, c_int32, c_void_p]),
     "dls_copy_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64,
                               c_void_p]),
     "dls_broadcast_row": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_void_p]),

@@ -263,6 +263,28 @@ class WaveExecutor:
                 return v
         return 1
 
+    def reconstruct_wave(self, segments: Sequence[Tuple[int, int, int, Sequence[int]]]):
+        """`reconstruct_from_chunks` for every task of the wave (dasklearn/functions.py:142-146 ->
+        ChunkManager.reconstruct_model, simulation/conflux/chunk_manager.py:34-53): `segments` holds, per
+        (task, chunk index), (output slot, first column, length, contributor slots in arrival order)."""
+        if len(segments) == 0:
+            return
+        ptr = np.zeros(len(segments) + 1, dtype=np.int32)
+        src: List[int] = []
+        outs = set()
+        for i, (o, c0, ln, ss) in enumerate(segments):
+            src.extend(int(x) for x in ss)
+            ptr[i + 1] = len(src)
+            outs.add(int(o))
+        if outs & set(src):
+            raise DlsError("reconstruct wave would overwrite one of its own inputs")
+        d_ptr, d_src, d_out, d_c0, d_len = self._upload(
+            ptr, np.asarray(src, dtype=np.int32), np.asarray([s[0] for s in segments], dtype=np.int32),
+            np.asarray([s[1] for s in segments], dtype=np.int64), np.asarray([s[2] for s in segments], dtype=np.int32))
+        K.chunk_mean(self.X, self.X, d_ptr, d_src, d_out, d_c0, d_len, max(s[2] for s in segments),
+                     int(np.diff(ptr).max()))
+        self.stats["chunk_segments"] = self.stats.get("chunk_segments", 0) + len(segments)
+
     def test_wave(self, slots: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
         """(accuracy %, mean loss) per slot on the whole test split
         (ModelEvaluator.evaluate_accuracy, dasklearn/model_evaluator.py:26-64)."""

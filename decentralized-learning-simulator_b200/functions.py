@@ -1,6 +1,7 @@
-"""API-compatible task entry points: `train`, `compute_gradient`, `gradient_update`, `aggregate`, `test`
+"""API-compatible task entry points: `train`, `compute_gradient`, `gradient_update`, `aggregate`, `test`,
+`chunk`, `reconstruct_from_chunks`
 with the signature `f(settings, params) -> [result]` of the reference (dasklearn/functions.py:28-77,
-80-86, 89-106, 109-133), looked up by name by the worker loop (`globals()[func_name]`, dasklearn/worker.py:27-31).
+80-86, 89-106, 109-133, 136-146), looked up by name by the worker loop (`globals()[func_name]`, dasklearn/worker.py:27-31).
 
 Differences that the DAG format hides: results are opaque `RowHandle`s (rows of the stacked
 HBM tensor) instead of `nn.Module`s, and the dataset is a device-resident `DeviceDataset`
@@ -102,6 +103,51 @@ def test(settings, params: Dict) -> List[RowHandle]:
     out = ex.alloc(1)[0]                # the reference returns a copy of the model (functions.py:132)
     ex.retain(out)
     ex.copy_rows([slot], [out])
+    return [RowHandle(ex, out)]
+
+
+class ChunkHandle:
+    """One piece of a chunked model: columns [c0, c1) of a row (the analogue of the tensor slices returned by
+    ChunkManager.chunk_model, simulation/conflux/chunk_manager.py:13-25)."""
+    __slots__ = ("executor", "slot", "c0", "c1")
+
+    def __init__(self, executor: WaveExecutor, slot: int, c0: int, c1: int):
+        self.executor, self.slot, self.c0, self.c1 = executor, slot, c0, c1
+
+    def numpy(self):
+        return self.executor.X[self.slot, self.c0:self.c1].cpu().numpy()
+
+
+def chunk(settings, params: Dict) -> List[ChunkHandle]:
+    """functions.py:136-140: `n` pieces of P // n elements of the flat model, the last takes the remainder.
+    The pieces alias the model's row (a copy of it, like the reference's slices of a fresh flat tensor)."""
+    ex = get_executor(settings)
+    n = int(params["n"])
+    out = ex.alloc(1)[0]
+    ex.retain(out)
+    ex.copy_rows([_slot_of(params["model"], ex)], [out])
+    P = ex.layout.P
+    size = P // n
+    return [ChunkHandle(ex, out, i * size, (i + 1) * size if i < n - 1 else P) for i in range(n)]
+
+
+def reconstruct_from_chunks(settings, params: Dict) -> List[RowHandle]:
+    """functions.py:142-146: params["chunks"][i] = the pieces received for chunk index i."""
+    chunks = params["chunks"]
+    ex = get_executor(settings)
+    out = ex.alloc(1)[0]
+    ex.retain(out)
+    segs = []
+    for idx, pieces in enumerate(chunks):
+        assert pieces, "No chunks received at index %d!" % idx            # chunk_manager.py:36
+        c0, c1 = pieces[0].c0, pieces[0].c1
+        for p in pieces:
+            if not isinstance(p, ChunkHandle) or p.executor is not ex or (p.c0, p.c1) != (c0, c1):
+                raise DlsError("piece %r does not belong to chunk index %d" % (p, idx))
+        segs.append((out, c0, c1 - c0, [p.slot for p in pieces]))
+    if sum(s[2] for s in segs) != ex.layout.P:
+        raise DlsError("the pieces do not cover the model")
+    ex.reconstruct_wave(segs)
     return [RowHandle(ex, out)]
 
 

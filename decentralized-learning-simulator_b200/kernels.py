@@ -46,6 +46,17 @@ def agg_variant_fits(variant: int, n_rows: int, n_src_rows: int, nnz: int) -> bo
     return rc == 1
 
 
+def chunk_mean(X, Y, seg_ptr, seg_src_rows, seg_out_row, seg_col0, seg_len, max_len: int, max_contributors: int):
+    """reconstruct_from_chunks wave: per segment the torch-order mean of a column range over its contributor rows."""
+    _need_cuda(X, Y, seg_ptr, seg_src_rows, seg_out_row, seg_col0, seg_len)
+    assert seg_col0.dtype == torch.int64
+    rc = _lib.lib().dls_chunk_mean_f32(X.data_ptr(), X.stride(0), Y.data_ptr(), Y.stride(0), _i32(seg_ptr).data_ptr(),
+                                       _i32(seg_src_rows).data_ptr(), _i32(seg_out_row).data_ptr(),
+                                       seg_col0.data_ptr(), _i32(seg_len).data_ptr(), seg_len.numel(), int(max_len),
+                                       int(max_contributors), _stream())
+    _lib.check(rc, "dls_chunk_mean_f32")
+
+
 def copy_rows(X, Y, src_rows, dst_rows, P: int):
     _need_cuda(X, Y, src_rows, dst_rows)
     rc = _lib.lib().dls_copy_rows(X.data_ptr(), X.stride(0), Y.data_ptr(), Y.stride(0), _lib.ptr(src_rows),

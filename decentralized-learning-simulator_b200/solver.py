@@ -23,13 +23,13 @@ from ._lib import DlsError
 from .executor import RowHandle, WaveExecutor
 
 TRAIN_FUNCS = ("train",)
-SUPPORTED = ("train", "aggregate", "test", "compute_gradient", "gradient_update")
+SUPPORTED = ("train", "aggregate", "test", "compute_gradient", "gradient_update", "chunk", "reconstruct_from_chunks")
 
 
 class Wave:
     __slots__ = ("level", "func", "names", "peers", "rounds", "times", "steps", "in_slots", "out_slots",
                  "model_slots", "weights", "init_slots", "copy_src", "copy_dst", "release_after", "prepared",
-                 "xchg", "grad_slots")
+                 "xchg", "grad_slots", "segments")
 
     def __init__(self, level: int, func: str):
         self.level, self.func = level, func
@@ -49,6 +49,7 @@ class Wave:
         self.prepared = None
         self.xchg = None            # multi-GPU: halo exchange that precedes this wave
         self.grad_slots: List[int] = []   # compute_gradient: row receiving the gradient; gradient_update: row read
+        self.segments: List[Tuple[int, int, int, List[int]]] = []   # reconstruct_from_chunks: (out slot, col0, len, contributor slots)
 
 
 class BatchedSolver:
@@ -134,6 +135,16 @@ class BatchedSolver:
         self._value_slot = value_slot
         grad_slot: Dict[Tuple[str, int], int] = {}        # outputs of compute_gradient tasks also carry a gradient row
         self._grad_slot = grad_slot
+        chunk_range: Dict[Tuple[str, int], Tuple[int, int]] = {}   # outputs of chunk tasks: column range of the row
+
+        def chunk_bounds(n: int):
+            """ChunkManager.chunk_model (simulation/conflux/chunk_manager.py:13-25): n slices of P // n elements,
+            the last one takes the remainder."""
+            P = ex.layout.P
+            size = P // n
+            b = [(i * size, (i + 1) * size) for i in range(n)]
+            b[-1] = (b[-1][0], P)
+            return b
 
         def ref_of(r):
             """Placeholders are (task name, output index) tuples; the AD-PSGD client also emits bare task
@@ -251,6 +262,36 @@ class BatchedSolver:
                     w.grad_slots.append(g)
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
+                elif func == "chunk":
+                    # functions.py:136-140: the n pieces are views of the flat model = column ranges of its row;
+                    # output idx i aliases the input row, one reference per consuming edge
+                    src = ref_of(d["model"])
+                    s_in = value_slot[src]
+                    bounds = chunk_bounds(int(d["n"]))
+                    for ci, b in enumerate(bounds):
+                        value_slot[(name, ci)] = s_in
+                        chunk_range[(name, ci)] = b
+                    w.in_slots.append(s_in)
+                    w.out_slots.append(s_in)
+                    sim_refs[s_in] += keep
+                    consume(src, pending_release)
+                elif func == "reconstruct_from_chunks":
+                    # functions.py:142-146: per chunk index the mean over the pieces received for it
+                    lists = [[tuple(m) for m in c] for c in d["chunks"]]
+                    bounds = chunk_bounds(len(lists))
+                    slot = take()
+                    for ci, refs in enumerate(lists):
+                        if not refs:
+                            raise AssertionError("No chunks received at index %d!" % ci)     # chunk_manager.py:36
+                        for m in refs:
+                            if chunk_range.get(m) != bounds[ci]:
+                                raise RuntimeError("task %s: piece %r is not chunk %d of %d" % (name, m, ci, len(lists)))
+                        w.segments.append((slot, bounds[ci][0], bounds[ci][1] - bounds[ci][0],
+                                           [value_slot[m] for m in refs]))
+                        pending_release.extend(value_slot[m] for m in refs)
+                    w.out_slots.append(slot)
+                    sim_refs[slot] += keep
+                    value_slot[(name, 0)] = slot
                 else:                                        # test: identity on the model data path
                     src = ref_of(d["model"])
                     s_in = value_slot[src]
@@ -271,8 +312,8 @@ class BatchedSolver:
                 sim_refs[s] = n
                 if n == 0:
                     free.append(s)
-            level_waves = [by_func[f] for f in ("train", "compute_gradient", "gradient_update", "aggregate", "test")
-                           if f in by_func]
+            level_waves = [by_func[f] for f in ("train", "compute_gradient", "gradient_update", "aggregate",
+                                                "reconstruct_from_chunks", "chunk", "test") if f in by_func]
             for w in level_waves:
                 self._end_level_wave(li, w)
             yield self._level_waves(li, level_waves)
@@ -350,6 +391,10 @@ class BatchedSolver:
             ex.grad_wave(w.in_slots, w.grad_slots, w.peers, w.rounds)
         elif w.func == "gradient_update":
             ex.gradient_update_wave(w.in_slots, w.grad_slots, w.out_slots)
+        elif w.func == "reconstruct_from_chunks":
+            ex.reconstruct_wave(w.segments)
+        elif w.func == "chunk":
+            pass                                  # pieces are column ranges of the model's row: nothing to compute
         else:
             acc, loss = ex.test_wave(w.out_slots)
             for i, name in enumerate(w.names):

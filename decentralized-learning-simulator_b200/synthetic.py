@@ -264,3 +264,52 @@ def adpsgd_dag(n_pairs: int, rounds: int) -> List[Dict]:
                 [(agg_a, 0)])
             own[p_], own[a] = (gu, 0), (t, 0)
     return list(tasks.values())
+
+
+def conflux_dag(n: int, rounds: int, sample_size: int, n_chunks: int, seed: int = 0) -> List[Dict]:
+    """A Shatter/Conflux-shaped compute graph (dasklearn/simulation/conflux/client.py:93-222) in the reference's
+    task format: every round a sample of `sample_size` nodes trains, each splits its model with a `chunk`
+    task (n pieces, output idx = piece index) and sends the pieces to the next sample; a node of the next
+    sample starts a `reconstruct_from_chunks` task as soon as it holds enough pieces, so the contributor
+    set differs per chunk index (between 1 and sample_size pieces, in arrival order)."""
+    rs = np.random.RandomState(seed)
+    tasks: Dict[str, Dict] = {}
+
+    def add(name, func, data, inputs):
+        tasks[name] = {"name": name, "func": func, "data": data, "inputs": list(inputs), "outputs": []}
+        for src, idx in inputs:
+            tasks[src]["outputs"].append((name, idx))
+
+    cnt = {"train": 0, "chunk": 0, "rec": 0}
+    sample = sorted(rs.choice(n, sample_size, replace=False).tolist())
+    model_of = {p: (None, 0) for p in sample}
+    trains = [0] * n
+    for r in range(1, rounds + 1):
+        chunk_tasks = []
+        for p in sample:
+            cnt["train"] += 1
+            trains[p] += 1
+            tname = "train_%d" % cnt["train"]
+            prev = model_of[p]
+            add(tname, "train", {"model": prev, "round": trains[p], "time": r * 1000, "peer": p},
+                [] if prev[0] is None else [prev])
+            cnt["chunk"] += 1
+            cname = "chunk_%d" % cnt["chunk"]
+            add(cname, "chunk", {"model": (tname, 0), "round": r, "time": r * 1000 + 100, "peer": p, "n": n_chunks},
+                [(tname, 0)])
+            chunk_tasks.append(cname)
+        nxt = sorted(rs.choice(n, sample_size, replace=False).tolist())
+        model_of = {}
+        for q in nxt:
+            received = []
+            for ci in range(n_chunks):
+                k = int(rs.randint(1, sample_size + 1))
+                senders = rs.permutation(sample_size)[:k].tolist()
+                received.append([(chunk_tasks[s], ci) for s in senders])
+            cnt["rec"] += 1
+            rname = "reconstruct_from_chunks_%d" % cnt["rec"]
+            add(rname, "reconstruct_from_chunks", {"chunks": received, "round": r + 1, "time": r * 1000 + 500, "peer": q},
+                [m for c in received for m in c])
+            model_of[q] = (rname, 0)
+        sample = nxt
+    return list(tasks.values())

@@ -73,6 +73,27 @@ int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t ldy,
  * does), negative on bad arguments: lets the caller choose a variant without a trial launch. */
 int dls_agg_variant_fits(int32_t variant, int32_t n_rows, int32_t n_src_rows, int32_t nnz);
 
+/* ------------------------------------------------------------------------------------------
+ * reconstruct_from_chunks wave — replaces N calls of functions.reconstruct_from_chunks ->
+ * ChunkManager.reconstruct_model (dasklearn/functions.py:142-146,
+ * dasklearn/simulation/conflux/chunk_manager.py:34-53).  `functions.chunk` (functions.py:136-140,
+ * chunk_manager.py:12-25) needs no kernel: a chunk is a column range of a row.
+ *
+ * Segment s (one chunk index of one reconstructed model):
+ *   Y[seg_out_row[s], c0 : c0+len] = mean over e in [seg_ptr[s], seg_ptr[s+1]) of X[seg_src_rows[e], c0 : c0+len]
+ * with c0 = seg_col0[s], len = seg_len[s], evaluated in the summation order of
+ * torch.mean(torch.stack(pieces), dim=0) on the CPU (sequential over contributors with a 16-row cascade
+ * for the columns below the last multiple of 32 of the piece, four interleaved partial sums for the rest;
+ * sum divided by the contributor count) — bit-identical to the reference on the same pieces.
+ * max_len = largest seg_len, max_contributors = largest contributor count (<= 1024, else DLS_E_TOO_BIG).
+ * Output ranges of different segments must not overlap; X and Y may be the same allocation when no output
+ * row is also a contributor row of the call.  No alignment requirement (chunk bounds are arbitrary).
+ * ------------------------------------------------------------------------------------------ */
+int dls_chunk_mean_f32(const float *X, int64_t ldx, float *Y, int64_t ldy, const int32_t *seg_ptr,
+                       const int32_t *seg_src_rows, const int32_t *seg_out_row, const int64_t *seg_col0,
+                       const int32_t *seg_len, int32_t n_segs, int32_t max_len, int32_t max_contributors,
+                       void *stream);
+
 /* Row plumbing on the stacked tensor (replaces the pickle round-trip copies of
  * serialize_model/unserialize_model, dasklearn/models/__init__.py:9-16). */
 int dls_copy_rows(const float *X, int64_t ldx, float *Y, int64_t ldy, const int32_t *src_rows,

@@ -88,6 +88,10 @@ class OracleExecutor(WaveExecutor):
         for r, o in enumerate(out_rows.tolist()):
             self.X[o] = torch.from_numpy(Y[r])
 
+    def reconstruct_wave(self, segments):
+        for o, c0, ln, srcs in segments:
+            self.X[o, c0:c0 + ln] = torch.from_numpy(O.mean_stack([self.X[s, c0:c0 + ln].numpy() for s in srcs]))
+
     def test_wave(self, slots):
         acc, loss = [], []
         for s in slots:

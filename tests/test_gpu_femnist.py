@@ -1,7 +1,8 @@
-"""FEMNIST CNN train / grad / test waves (CUDA fp32 path) against the CPU restatement in
-oracle/oracle.py.  The reference cannot import its own FEMNIST model (dasklearn/models/femnist.py:5
-needs a module that is not in the tree), so this parity is against a restatement of
-dasklearn/models/femnist.py:45-85 + model_trainer.py:99-126 — "parity unpinned"."""
+"""FEMNIST CNN train / grad / test waves (CUDA fp32 path) against the oracle (oracle/oracle.py) and against
+tests/golden/femnist_kat.npz, which the reference's own `CNN` and `SGDOptimizer` classes produced
+(dasklearn/models/femnist.py:45-85 is importable once the missing module dasklearn.datasets.femnist is supplied
+as a two-constant shim; the loop around it is model_trainer.py:99-126, which the reference's trainer itself
+refuses to run for this dataset)."""
 import numpy as np
 import pytest
 import torch
@@ -132,3 +133,59 @@ def test_solver_dpsgd_femnist(cuda, tmp_path):
     for peer, rnd, t_us, a, l in acc:
         got = open(str(tmp_path / ("accuracies_%d.csv" % peer))).read().strip().split("\n")[1].split(",")
         assert got[1] == "femnist" and abs(float(got[7]) - a) <= 100.0 / n_test + 1e-9 and abs(float(got[8]) - l) < 1e-3
+
+
+def test_pinned_to_reference_model_class(cuda, golden_dir):
+    """The CUDA FEMNIST kernels against outputs of the reference's OWN `CNN` + `SGDOptimizer` classes
+    (tests/golden/femnist_kat.npz, make_golden.py gen_femnist): logits, loss, gradient of one minibatch, and
+    three optimizer steps with a partial last batch (32, 32, 20)."""
+    import json, os
+    g = np.load(os.path.join(golden_dir, "femnist_kat.npz"))
+    meta = json.loads(str(g["meta"]))
+    from dls_b200.models import initial_row
+    init = initial_row(L, meta["seed"]).numpy()
+    assert np.array_equal(init[:L.P:64], g["init_strided"])
+    imgs, labs = synthetic.make_images(meta["n_i"], 28, 1, 62, seed=meta["image_seed"])
+    order = synthetic.minibatch_permutation(meta["seed"], meta["peer"], meta["round"], meta["n_i"])
+    B = meta["batch"]
+    o1 = L.offset("fc1.weight")
+    keep = np.ones(L.P, dtype=bool)
+    keep[o1:o1 + 512 * 3136] = False
+    keep[o1:o1 + 512 * 3136:meta["fc1_stride"]] = True
+    d_img = torch.from_numpy(imgs.reshape(-1, 784)).to(cuda)
+    d_lab = torch.from_numpy(labs.astype(np.int64)).to(cuda)
+    Xd = torch.from_numpy(init[None, :].copy()).to(cuda)
+    row0 = torch.zeros(1, dtype=torch.int32, device=cuda)
+    # logits of the first minibatch through the test wave
+    sel = order[:B]
+    logits = torch.zeros((1, B, 62), device=cuda)
+    K.eval_wave(L, Xd, row0, d_img[torch.from_numpy(sel.astype(np.int64)).to(cuda)].contiguous(),
+                d_lab[torch.from_numpy(sel.astype(np.int64)).to(cuda)].contiguous(), K.Workspace(cuda),
+                out_logits=logits)
+    assert np.abs(logits[0].cpu().numpy() - g["logits"]).max() < 1e-5
+    # gradient + loss of the first minibatch
+    G = torch.zeros((1, L.ld), device=cuda)
+    loss = torch.zeros(1, device=cuda)
+    idx0 = torch.from_numpy(sel.astype(np.int32)[None, :].copy()).to(cuda)
+    K.grad_wave(L, Xd, G, row0, d_img, d_lab, idx0, torch.tensor([B], dtype=torch.int32, device=cuda), B,
+                K.Workspace(cuda), loss_out=loss)
+    torch.cuda.synchronize()
+    assert abs(float(loss[0]) - float(g["loss"])) < 1e-5
+    Gh = G[0, :L.P].cpu().numpy()
+    assert rel(Gh[keep], g["grad_kept"]) < 1e-4
+    assert abs(np.linalg.norm(Gh.astype(np.float64)) - float(g["grad_l2"])) < 1e-4 * float(g["grad_l2"])
+    # three optimizer steps (lr 0.004, momentum 0), partial last batch
+    counts = meta["counts"]
+    idx = -np.ones((3, 1, B), np.int32)
+    for s, c in enumerate(counts):
+        idx[s, 0, :c] = order[s * B: s * B + c]
+    lo = torch.zeros((3, 1), device=cuda)
+    K.train_wave(L, Xd, None, row0, row0, torch.ones(1, dtype=torch.uint8, device=cuda), d_img, d_lab,
+                 torch.from_numpy(idx).to(cuda), torch.tensor(counts, dtype=torch.int32, device=cuda).reshape(3, 1), B,
+                 meta["lr"], meta["momentum"], meta["wd"], K.Workspace(cuda), loss_out=lo)
+    torch.cuda.synchronize()
+    after = Xd[0, :L.P].cpu().numpy()
+    assert rel(after[keep], g["after_kept"]) < 1e-5
+    assert rel(after[keep] - init[:L.P][keep], g["after_kept"] - init[:L.P][keep]) < 1e-3
+    assert abs(after.astype(np.float64).sum() - float(g["after_sum"])) < 1e-2
+    assert np.abs(lo[:, 0].cpu().numpy() - g["step_losses"]).max() < 1e-4

@@ -326,3 +326,108 @@ def test_split_train_wave_equals_small_waves(cuda, tmp_path, precision):
     assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32))
     assert np.array_equal(out[0][1].view(np.uint32), out[1][1].view(np.uint32))
     assert not np.array_equal(out[0][0][0], out[0][0][159])
+
+
+@pytest.mark.parametrize("precision", [0, 1])
+def test_c1_matches_reference(cuda, golden_dir, tmp_path, precision):
+    """BASELINE config C1 solved by the reference itself (16 nodes, 4-regular, 5 rounds x 5 local steps, test at
+    round 5; tests/golden/make_golden.py gen_c1), compared after the whole 25-step trajectory.
+    Measured on a B200 (scripts/parity_diag.py): fp32 path 3.5e-4 .. 5.8e-4 relative per node — the oracle run
+    with 4 torch threads instead of the fixture's 1 already differs from the fixture by 2.7e-4 .. 3.6e-4,
+    rounding differences grow along a momentum-SGD trajectory — and bf16 tensor-core path 1.2e-3 .. 1.45e-3.
+    The north-star bound of 1e-3 is per ROUND (same starting point), asserted in test_c2_round_against_oracle,
+    test_train_kat_two_rounds and the 3-round mini graph; here the bounds are 8e-4 (fp32) and 2e-3 (bf16) for
+    five rounds.  Accuracy: the models are near chance (20 %) after 25 steps, where single predictions flip
+    with the last bits of the logits, so the mean over the 16 nodes is held to 0.5 pp (fp32) / 1 pp (bf16) and
+    single nodes to 6 / 13 of the 256 test images; the 0.5 pp criterion per model is asserted on trained
+    models in test_accuracy_trajectory_fp32_bf16_oracle."""
+    g = np.load(os.path.join(golden_dir, "dpsgd_c1.npz"))
+    meta = json.loads(str(g["meta"]))
+    dag = pickle.load(open(os.path.join(golden_dir, "dpsgd_c1_dag.pkl"), "rb"))
+    n = meta["n"]
+    st = SessionSettings(participants=n, seed=meta["seed"], data_dir=str(tmp_path), precision=precision,
+                         learning=LearningSettings(0.002, 0.9, 0.0, 32, meta["local_steps"]))
+    ds = DeviceDataset.synthetic(L, n, meta["n_i"], meta["n_test"], cuda, seed=meta["seed"])
+    ex = WaveExecutor(st, ds)
+    solver = BatchedSolver(ex, dag).plan()
+    assert [w.func for w in solver.waves] == ["train", "aggregate"] * 5 + ["test"]
+    res = solver.run()
+    final = {int(name.split("_")[1]): h[0].numpy() for name, h in res.items()}
+    tol = 8e-4 if precision == 0 else 2e-3
+    assert rel(final[0], g["final_node0"]) < tol
+    assert rel(final[11], g["final_node11"]) < tol
+    acc_got, acc_want = [], []
+    for peer in range(n):
+        assert rel(final[peer][::16], g["final_strided"][peer]) < tol
+        l2 = np.sqrt((final[peer].astype(np.float64) ** 2).sum())
+        assert abs(l2 - g["final_l2"][peer]) < tol * g["final_l2"][peer]
+        want = str(g["acc_csv"][peer]).strip().split("\n")
+        got = open(os.path.join(str(tmp_path), "accuracies_%d.csv" % peer)).read().strip().split("\n")
+        assert got[0] == want[0] and len(got) == len(want) == 2
+        gw, ww = got[1].split(","), want[1].split(",")
+        assert gw[:7] == ww[:7]
+        acc_got.append(float(gw[7])); acc_want.append(float(ww[7]))
+        assert abs(acc_got[-1] - acc_want[-1]) <= (6 if precision == 0 else 13) * 100.0 / meta["n_test"] + 1e-9
+        assert abs(float(gw[8]) - float(ww[8])) < (3e-3 if precision == 0 else 2e-2)
+    assert abs(np.mean(acc_got) - np.mean(acc_want)) <= (0.5 if precision == 0 else 1.0), (acc_got, acc_want)
+    assert ex.stats["train_steps"] == n * meta["rounds"] * meta["local_steps"]
+
+
+@pytest.mark.parametrize("precision", [0, 1])
+def test_c2_round_against_oracle(cuda, golden_dir, tmp_path, precision):
+    """C2 size (256 nodes, k = 8, the reference DES's own graph), first round, against the oracle: the trained
+    rows of 36 nodes (four aggregates' complete neighbourhoods) and those four aggregated rows within the
+    train tolerance, and ALL 256 aggregated rows bit-exact given the GPU's own trained rows."""
+    import gzip
+    from oracle import oracle as O
+    dag = pickle.load(gzip.open(os.path.join(golden_dir, "dpsgd_c2_dag.pkl.gz"), "rb"))
+    n, n_i, steps = 256, 64, 2
+    by_name = {t["name"]: t for t in dag}
+    level0 = [t for t in dag if t["func"] == "train" and not t["inputs"]]
+    aggs1 = [t for t in dag if t["func"] == "aggregate" and all(by_name[m[0]] in level0 for m in t["data"]["models"])]
+    assert len(level0) == 256 and len(aggs1) == 256
+    first_round = level0 + aggs1
+    for t in first_round:                       # cut the graph after the first aggregate level
+        t = dict(t)
+    sub = []
+    keep = {t["name"] for t in first_round}
+    for t in first_round:
+        sub.append({"name": t["name"], "func": t["func"], "data": t["data"], "inputs": list(t["inputs"]),
+                    "outputs": [o for o in t["outputs"] if o[0] in keep]})
+    st = SessionSettings(participants=n, seed=42, data_dir=str(tmp_path), precision=precision,
+                         learning=LearningSettings(0.002, 0.9, 0.0, 32, steps))
+    ds = DeviceDataset.synthetic(L, n, n_i, 16, cuda, seed=42)
+    ex = WaveExecutor(st, ds)
+    solver = BatchedSolver(ex, sub).plan()
+    assert [w.func for w in solver.waves] == ["train", "aggregate"]
+    solver.run_wave(solver.waves[0])
+    torch.cuda.synchronize()
+    trained = {name: ex.X[slot, :L.P].cpu().numpy() for name, slot in zip(solver.waves[0].names, solver.waves[0].out_slots)}
+    solver.run_wave(solver.waves[1])
+    torch.cuda.synchronize()
+    agg = {name: ex.X[slot, :L.P].cpu().numpy() for name, slot in zip(solver.waves[1].names, solver.waves[1].out_slots)}
+    # (1) all 256 aggregates, bit-exact on the GPU's trained rows
+    for t in aggs1:
+        want = O.fedavg_numpy([trained[m[0]] for m in t["data"]["models"]])
+        assert np.array_equal(agg[t["name"]].view(np.uint32), want.view(np.uint32)), t["name"]
+    # (2) four complete neighbourhoods through the oracle's train + aggregate
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    init = O.initial_row(L, 42)
+    tol = 3e-4 if precision == 0 else 1e-3
+    torch.set_num_threads(4)
+    oracle_trained = {}
+    for t in aggs1[::64]:
+        assert len(t["data"]["models"]) == 9
+        for m in t["data"]["models"]:
+            if m[0] in oracle_trained:
+                continue
+            peer = by_name[m[0]]["data"]["peer"]
+            idx, cnt = synthetic.minibatch_index(42, [peer], [1], n_i, 32, steps)
+            row, _, _ = O.train_task(L, init, None, imgs[peer], labs[peer], idx[0], cnt[0], 0.002, 0.9, 0.0)
+            oracle_trained[m[0]] = row[:L.P]
+            # the update (row - init) is what training computed: hold it, not just the row, to the tolerance
+            assert rel(trained[m[0]], row[:L.P]) < tol, m[0]
+            assert rel(trained[m[0]] - init[:L.P], row[:L.P] - init[:L.P]) < (2e-3 if precision == 0 else 5e-2), m[0]
+        want = O.fedavg_numpy([oracle_trained[m[0]] for m in t["data"]["models"]])
+        assert rel(agg[t["name"]], want) < tol, t["name"]
+    assert len(oracle_trained) >= 32

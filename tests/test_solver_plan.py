@@ -120,7 +120,7 @@ def test_shared_input_forces_copy_and_churn_fan_in():
 def test_unknown_function_and_cycle():
     with pytest.raises(RuntimeError, match="not found"):
         BatchedSolver(PlanOnlyExecutor(2, settings(1)),
-                      [{"name": "x", "func": "chunk", "data": {"peer": 0}, "inputs": [], "outputs": []}])
+                      [{"name": "x", "func": "push_model", "data": {"peer": 0}, "inputs": [], "outputs": []}])
     cyc = [{"name": "a", "func": "test", "data": {"model": ("b", 0), "peer": 0}, "inputs": [("b", 0)], "outputs": [("b", 0)]},
            {"name": "b", "func": "test", "data": {"model": ("a", 0), "peer": 0}, "inputs": [("a", 0)], "outputs": [("a", 0)]}]
     with pytest.raises(RuntimeError, match="cycle"):
@@ -175,3 +175,32 @@ def test_adpsgd_shaped_graph_solves_like_the_sequential_oracle(tmp_path):
         # only the four sink rows stay referenced: gradient rows and intermediate models were released
         assert int((ex.refs > 0).sum()) == 4
         assert [w.func for w in solver.waves].count("compute_gradient") == 2
+
+
+def test_conflux_chunk_graph_against_oracle():
+    """chunk / reconstruct_from_chunks waves (functions.py:136-146): the planner's aliasing of pieces to
+    column ranges, per-edge reference counts and segment lists, executed with oracle arithmetic on CPU,
+    must reproduce the oracle's task-by-task solve bit for bit."""
+    import torch
+    from oracle import oracle as O
+    from cpu_standin import OracleExecutor
+    from dls_b200.layout import GNLENET as L
+    n, n_i = 6, 32
+    dag = synthetic.conflux_dag(n, rounds=2, sample_size=3, n_chunks=5, seed=1)
+    assert {t["func"] for t in dag} == {"train", "chunk", "reconstruct_from_chunks"}
+    imgs, labs = synthetic.make_partitions(n, n_i, 32, 3, 10)
+    timg, tlab = synthetic.make_test_split(8, 32, 3, 10)
+    st = SessionSettings(participants=n, seed=42, learning=LearningSettings(0.002, 0.9, 0.0, 32, 1))
+    torch.set_num_threads(1)
+    ex = OracleExecutor(st, imgs, labs, timg, tlab, list(range(n)), n_i)
+    solver = BatchedSolver(ex, dag).plan()
+    assert any(w.func == "reconstruct_from_chunks" and len(w.segments) == 5 * len(w.names) for w in solver.waves)
+    res = solver.run()
+    sinks, _ = O.solve_dag(L, dag, imgs, labs, timg, tlab, seed=42, batch=32, local_steps=1, lr=0.002, mu=0.9,
+                           wd=0.0, n_i=n_i, minibatch_permutation=synthetic.minibatch_permutation)
+    assert sorted(res) == sorted(sinks) and len(sinks) == 3
+    for name, row in sinks.items():
+        got = ex.X[res[name][0].slot].numpy()
+        assert np.array_equal(got[:L.P].view(np.uint32), row[:L.P].view(np.uint32)), name
+    # every row went back to the pool except the sinks
+    assert int((ex.refs > 0).sum()) == len(sinks)

@@ -29,6 +29,7 @@ SIGNATURES = {
                                    c_void_p, c_int32, c_int32, c_int32, c_void_p]),
     "dls_copy_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64,
                               c_void_p]),
+    "dls_push_rows": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int64, c_void_p]),
     "dls_broadcast_row": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int64, c_void_p]),
     "dls_gradient_update": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_float,
                                     c_float, c_void_p]),

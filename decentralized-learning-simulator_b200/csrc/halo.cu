@@ -1,0 +1,56 @@
+// Halo push for the multi-GPU aggregate wave: every rank writes the rows its neighbours on other GPUs need
+// straight into THEIR halo rows over NVLink (peer-mapped memory, plain 16-byte stores), one kernel, no staging
+// copy and no receive side.  The reference analogue is a pickled nn.Module sent broker to broker over ZeroMQ
+// (dasklearn/broker.py:207-219).
+//
+// Stores to a peer are posted (fire and forget), so a grid sized to the SM count keeps many 16-byte stores in
+// flight per SM; loads come from local HBM.  The kernel ends with a system-scope fence; the caller follows it
+// with a cross-GPU barrier before any rank reads its halo.
+#include "common.cuh"
+
+namespace dls {
+
+// grid = (column blocks, transfers); transfer e copies X[src_rows[e], 0:P) to the row at dst_ptrs[e].
+__global__ void __launch_bounds__(256)
+push_rows_kernel(const float *__restrict__ X, int64_t ldx, const int32_t *__restrict__ src_rows,
+                 const uint64_t *__restrict__ dst_ptrs, int64_t P4)
+{
+    const int e = blockIdx.y;
+    const float4 *src = reinterpret_cast<const float4 *>(X + (int64_t)src_rows[e] * ldx);
+    float4 *dst = reinterpret_cast<float4 *>(dst_ptrs[e]);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // four independent 16-byte loads in flight per thread before the stores are issued
+    for (; c + 3 * stride < P4; c += 4 * stride) {
+        const float4 a = ldg_stream4(reinterpret_cast<const float *>(src + c));
+        const float4 b = ldg_stream4(reinterpret_cast<const float *>(src + c + stride));
+        const float4 d = ldg_stream4(reinterpret_cast<const float *>(src + c + 2 * stride));
+        const float4 f = ldg_stream4(reinterpret_cast<const float *>(src + c + 3 * stride));
+        dst[c] = a; dst[c + stride] = b; dst[c + 2 * stride] = d; dst[c + 3 * stride] = f;
+    }
+    for (; c < P4; c += stride) dst[c] = ldg_stream4(reinterpret_cast<const float *>(src + c));
+    __threadfence_system();
+}
+
+}  // namespace dls
+
+extern "C" int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_rows, const uint64_t *dst_ptrs,
+                             int32_t n_transfers, int64_t P, void *stream)
+{
+    if (!X || !src_rows || !dst_ptrs || n_transfers < 0 || P <= 0 || ldx < P) return DLS_E_ARG;
+    if (!dls::aligned16(X) || (ldx & 3)) return DLS_E_ALIGN;
+    if (n_transfers == 0) return 0;
+    if (n_transfers > 65535) return DLS_E_TOO_BIG;
+    const int64_t P4 = (P + 3) / 4;                       // rows are padded to a multiple of 4 floats (ld % 4 == 0)
+    int sms = dls::num_sms();
+    if (sms <= 0) sms = 148;
+    // enough CTAs to cover the SMs several times over even for a handful of transfers
+    int bx = (int)((P4 + 4 * 256 - 1) / (4 * 256));
+    const int want = (8 * sms + n_transfers - 1) / n_transfers;
+    if (bx > want) bx = want;
+    if (bx < 1) bx = 1;
+    dim3 grid((unsigned)bx, (unsigned)n_transfers);
+    dls::push_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ldx, src_rows, dst_ptrs, P4);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}

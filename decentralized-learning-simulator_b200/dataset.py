@@ -38,8 +38,21 @@ class DeviceDataset:
 
     @classmethod
     def synthetic(cls, layout: ModelLayout, n_nodes: int, n_i: int, n_test: int, device, seed: int = 42,
-                  data_seed: int = 1234, node_ids: Optional[Sequence[int]] = None) -> "DeviceDataset":
-        """Synthetic partitions for `node_ids` (default: all `n_nodes`), identical on every rank."""
+                  data_seed: int = 1234, node_ids: Optional[Sequence[int]] = None,
+                  per_node_seed: bool = False) -> "DeviceDataset":
+        """Synthetic partitions for `node_ids` (default: all `n_nodes`), identical on every rank.
+        `per_node_seed`: node p's partition is `make_images(n_i, seed=data_seed + p)` — generated node by node
+        (host memory stays O(one partition)), for large runs that are not compared with a whole-population fixture."""
+        if per_node_seed:
+            ids = list(node_ids) if node_ids is not None else list(range(n_nodes))
+            imgs = np.empty((len(ids), n_i, layout.img_hw, layout.img_hw, layout.img_c), dtype=np.uint8)
+            labs = np.empty((len(ids), n_i), dtype=np.int64)
+            for i, p in enumerate(ids):
+                imgs[i], labs[i] = synthetic.make_images(n_i, layout.img_hw, layout.img_c, layout.num_classes,
+                                                         seed=data_seed + int(p))
+            timg, tlab = synthetic.make_test_split(n_test, layout.img_hw, layout.img_c, layout.num_classes,
+                                                   seed=data_seed)
+            return cls(imgs, labs, timg, tlab, device, seed, node_ids=node_ids)
         imgs, labs = synthetic.make_partitions(n_nodes, n_i, layout.img_hw, layout.img_c, layout.num_classes,
                                                seed=data_seed)
         timg, tlab = synthetic.make_test_split(n_test, layout.img_hw, layout.img_c, layout.num_classes,

@@ -64,6 +64,15 @@ def copy_rows(X, Y, src_rows, dst_rows, P: int):
     _lib.check(rc, "dls_copy_rows")
 
 
+def push_rows(X, src_rows, dst_ptrs, P: int):
+    """Halo push: X[src_rows[e]] -> the (possibly peer-GPU) row at device address dst_ptrs[e] (int64 tensor)."""
+    _need_cuda(X, src_rows, dst_ptrs)
+    assert dst_ptrs.dtype == torch.int64 and dst_ptrs.numel() == src_rows.numel()
+    rc = _lib.lib().dls_push_rows(X.data_ptr(), X.stride(0), _i32(src_rows).data_ptr(), dst_ptrs.data_ptr(),
+                                  src_rows.numel(), P, _stream())
+    _lib.check(rc, "dls_push_rows")
+
+
 def broadcast_row(src, Y, dst_rows, P: int):
     _need_cuda(src, Y, dst_rows)
     rc = _lib.lib().dls_broadcast_row(src.data_ptr(), Y.data_ptr(), Y.stride(0), dst_rows.data_ptr(),

@@ -84,8 +84,18 @@ def topology_from_dag(serialized_tasks: Sequence[Dict], n: int) -> List[List[int
 
 
 class DistributedSolver(BatchedSolver):
+    """`transport`: how rows cross GPUs at an aggregate level.
+      "a2a"  — pack (`dls_copy_rows`) + one `all_to_all_single` (NCCL over NVLink; gloo in the CPU tests) into the
+               halo rows after the pool;
+      "push" — one-sided: every rank writes the rows its neighbours need straight into THEIR halo rows over
+               NVLink (`dls_push_rows`, peer-mapped symmetric memory), then one cross-GPU barrier; no pack copy,
+               no receive side.  Needs the executor's X in symmetric memory (`WaveExecutor.enable_symmetric`);
+      "auto" — "push" on NCCL process groups when symmetric memory can be set up on every rank, else "a2a"."""
+
+    HALO_VERSIONS = 2        # push: rows of one remote node that may be live in a halo at one level
+
     def __init__(self, executor, serialized_tasks, rank: int, world: int, owner_of: Sequence[int],
-                 on_sink=None, agg_variant: int = 0, group=None):
+                 on_sink=None, agg_variant: int = 0, group=None, transport: str = "auto"):
         owner_of = np.asarray(owner_of, dtype=np.int32)
         owned = [int(p) for p in np.nonzero(owner_of == rank)[0]]
         super().__init__(executor, serialized_tasks, on_sink=on_sink, owned_peers=owned, agg_variant=agg_variant)
@@ -95,53 +105,132 @@ class DistributedSolver(BatchedSolver):
         self.max_halo = 0
         self.max_send = 0
         self.halo_bytes = 0
+        self.transport = self._choose_transport(transport)
+
+    def _choose_transport(self, want: str) -> str:
+        ex = self.ex
+        have = getattr(ex, "transport", None)
+        if have is not None:                          # settled once per executor (a collective decision)
+            if want not in ("auto", have):
+                raise RuntimeError("executor already uses transport %r" % have)
+            return have
+        if want == "a2a" or not hasattr(ex, "enable_symmetric"):
+            got = "a2a"
+        else:
+            import torch.distributed as dist
+            ok = dist.is_initialized() and dist.get_backend(self.group) == "nccl"
+            if ok:
+                counts = np.bincount(self.owner_of, minlength=self.world)
+                n_local_max = int(counts.max())
+                halo_cap = self.HALO_VERSIONS * int(len(self.owner_of) - counts.min())
+                ok = ex.enable_symmetric(self.group, pool_cap=3 * n_local_max + 8, halo_cap=halo_cap)
+            if want == "push" and not ok:
+                raise RuntimeError("transport 'push' needs NCCL and symmetric memory on every rank")
+            got = "push" if ok else "a2a"
+        ex.transport = got
+        return got
 
     # -- planning hooks ---------------------------------------------------------------------
-    # Every rank holds the whole task list, but its planning work is O(own tasks + cut edges): task owners
-    # and levels are looked up in dictionaries built once, and the rows this rank must SEND are found from
-    # the `outputs` lists of its own tasks instead of scanning every other rank's aggregate tasks.
+    # Every rank holds the whole task list.  One cheap pass over it settles the levels and the levels at which
+    # ANY rank has a cut edge (the exchange is entered by every rank at exactly those levels, also by a rank
+    # that neither sends nor receives there: irregular graphs, world > 2); everything else a rank plans is
+    # O(own tasks + cut edges): the rows to SEND are found from the `outputs` lists of its own tasks.
     def _owner_of_task(self, name: str) -> int:
         return self._task_owner[name]
 
     def levelise(self):
-        levels = super().levelise()
         tasks, me = self.tasks, self.rank
         owner_list = self.owner_of.tolist()       # plain ints: numpy scalar indexing is ~10x slower per lookup
-        self._task_owner = {name: owner_list[t["data"]["peer"]] for name, t in tasks.items()}
-        own = self._task_owner
-        level_of = {}
-        for li, names in enumerate(levels):
-            for n in names:
-                level_of[n] = li
-        remote = {}                               # level -> [(consumer rank, my value consumed there)], one per edge
-        # Levels at which ANY rank has a cut edge: the exchange is a collective over the whole group, so every
-        # rank must enter it at exactly these levels, also when it neither sends nor receives there itself
-        # (irregular graphs: async gossip / AD-PSGD levels, world > 2).
+        own: Dict[str, int] = {}
+        level_of: Dict[str, int] = {}
+        own_get, lvl_get = own.__getitem__, level_of.__getitem__
         xchg_levels = set()
-        for name, t in tasks.items():
-            mine = own[name]
-            if mine != me:
-                for cons, _ in t["outputs"]:
-                    if own[cons] != mine:
-                        xchg_levels.add(level_of[cons])
-                continue
-            for src, _ in t["inputs"]:
-                if own[src] != me and t["func"] != "aggregate":
-                    raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % name)
-            for cons, idx in t["outputs"]:
+        mine: List[str] = []
+        try:
+            # ONE pass in list order (creation order is topological, see BatchedSolver.levelise): owner, level,
+            # and whether the task has an input produced on another GPU
+            for name, t in tasks.items():
+                o = owner_list[t["data"]["peer"]]
+                own[name] = o
+                if o == me:
+                    mine.append(name)
+                ins = t["inputs"]
+                if not ins:
+                    level_of[name] = 0
+                    continue
+                if len(ins) == 1:
+                    src = ins[0][0]
+                    l = level_of[src] + 1
+                    cut = own[src] != o
+                else:
+                    names = next(zip(*ins))
+                    l = 1 + max(map(lvl_get, names))
+                    owners = set(map(own_get, names))
+                    cut = len(owners) > 1 or o not in owners
+                level_of[name] = l
+                if cut:
+                    if t["func"] != "aggregate":
+                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % name)
+                    xchg_levels.add(l)
+            self._level_of = level_of
+            n_levels = max(level_of.values()) + 1 if level_of else 0
+        except KeyError:                          # not in topological order: generic levelisation, then the cut scan
+            own = {name: owner_list[t["data"]["peer"]] for name, t in tasks.items()}
+            n_levels = len(super()._levelise_kahn())
+            level_of = self._level_of
+            mine = [n for n in tasks if own[n] == me]
+            xchg_levels = set()
+            for name, t in tasks.items():
+                if any(own[src] != own[name] for src, _ in t["inputs"]):
+                    if t["func"] != "aggregate":
+                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % name)
+                    xchg_levels.add(level_of[name])
+        self._task_owner = own
+        remote = {}                               # level -> [(consumer rank, my value consumed there)], one per edge
+        for name in mine:
+            for cons, idx in tasks[name]["outputs"]:
                 q = own[cons]
                 if q != me:
-                    if tasks[cons]["func"] != "aggregate":
-                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % cons)
                     remote.setdefault(level_of[cons], []).append((q, (name, idx)))
-                    xchg_levels.add(level_of[cons])
         self._remote = remote
         self._xchg_levels = xchg_levels
+        self._xchg_index = {l: i for i, l in enumerate(sorted(xchg_levels))}
+        if self.transport == "push":
+            # static halo numbering: node p's row lands in slot (index of p among the nodes rank q does not own)
+            self._remote_index = [None] * self.world
         # the base planner only looks at this rank's tasks
-        return [[n for n in names if own[n] == me] for names in levels]
+        out = [[] for _ in range(n_levels)]
+        for n in mine:
+            out[level_of[n]].append(n)
+        return out
 
     def _halo_key(self, m):
         return (int(self.tasks[m[0]]["data"]["peer"]), m[0], m[1])
+
+    def _remote_idx(self, q: int) -> np.ndarray:
+        """index of node p among the nodes NOT owned by rank q (push transport: halo slot numbering of rank q)."""
+        r = self._remote_index[q]
+        if r is None:
+            not_q = (self.owner_of != q)
+            r = (np.cumsum(not_q) - 1).astype(np.int64)
+            self._remote_index[q] = r
+        return r
+
+    def _push_slots(self, q: int, rows):
+        """Halo slots (without the parity offset) on rank q for `rows` = sorted [(peer, task, idx)] coming from ONE
+        source rank: slot = remote index of the peer + version * n_remote, the version counting rows of the same
+        node within this level.  Receiver and sender evaluate this on the same list, so they agree."""
+        ridx = self._remote_idx(q)
+        n_remote = int((self.owner_of != q).sum())
+        out, last, v = [], None, 0
+        for peer, _, _ in rows:
+            v = v + 1 if peer == last else 0
+            last = peer
+            if v >= self.HALO_VERSIONS:
+                raise RuntimeError("push transport: more than %d live rows of node %d needed by rank %d at one level; "
+                                   "use transport='a2a'" % (self.HALO_VERSIONS, peer, q))
+            out.append(int(ridx[peer]) + v * n_remote)
+        return out
 
     def _begin_level(self, level: int, names: List[str], pending_release: List[int]):
         me, own, tasks = self.rank, self._task_owner, self.tasks
@@ -152,33 +241,56 @@ class DistributedSolver(BatchedSolver):
             if t["func"] != "aggregate":
                 continue
             for m in t["data"]["models"]:
-                m = tuple(m)
                 r = own[m[0]]
                 if r != me:
-                    recv[r].add(m)
+                    recv[r].add(m if type(m) is tuple else tuple(m))
+        vs = self._value_slot
         for q, m in self._remote.get(level, ()):              # one reference per consuming remote task
-            pending_release.append(self._value_slot[m])
+            pending_release.append(vs[m])
             send[q].add(m)
         # both ends order a (source rank -> destination rank) row list the same way: by producer peer, task, index
-        recv_l = [sorted(x, key=self._halo_key) for x in recv]
-        send_l = [sorted(x, key=self._halo_key) for x in send]
+        key = self._halo_key
+        recv_l = [sorted(map(key, x)) for x in recv]
+        send_l = [sorted(map(key, x)) for x in send]
         self._halo_of = {}
+        n_recv = sum(len(x) for x in recv_l)
+        n_send = sum(len(x) for x in send_l)
+        if not (n_recv or n_send or level in self._xchg_levels):
+            return
+        if self.transport == "push":
+            ex = self.ex
+            parity = self._xchg_index[level] & 1
+            for r in range(self.world):
+                if recv_l[r]:
+                    for (peer, tn, idx), slot in zip(recv_l[r], self._push_slots(me, recv_l[r])):
+                        self._halo_of[(tn, idx)] = parity * ex.halo_cap + slot
+            send_slots, dst = [], []
+            row_bytes = ex.layout.ld * 4
+            for q in range(self.world):
+                if send_l[q]:
+                    base = ex.peer_x_ptrs[q] + (ex.halo_base + parity * ex.halo_cap) * row_bytes
+                    for (peer, tn, idx), slot in zip(send_l[q], self._push_slots(q, send_l[q])):
+                        send_slots.append(vs[(tn, idx)])
+                        dst.append(base + slot * row_bytes)
+            self._level_xchg[level] = {"send_slots": send_slots, "dst_ptrs": dst, "n_recv": n_recv}
+            self.max_halo = max(self.max_halo, n_recv)
+            self.max_send = max(self.max_send, n_send)
+            return
         h = 0
         for r in range(self.world):                           # all_to_all output is ordered by source rank
-            for m in recv_l[r]:
-                self._halo_of[m] = h
+            for peer, tn, idx in recv_l[r]:
+                self._halo_of[(tn, idx)] = h
                 h += 1
-        n_send = sum(len(x) for x in send_l)
-        if h or n_send or level in self._xchg_levels:
-            self._level_xchg[level] = {"send_slots": [self._value_slot[m] for x in send_l for m in x],
-                                       "send_counts": [len(x) for x in send_l],
-                                       "recv_counts": [len(x) for x in recv_l]}
-            self.max_halo = max(self.max_halo, h)
-            self.max_send = max(self.max_send, n_send)
+        self._level_xchg[level] = {"send_slots": [vs[(tn, idx)] for x in send_l for _, tn, idx in x],
+                                   "send_counts": [len(x) for x in send_l],
+                                   "recv_counts": [len(x) for x in recv_l]}
+        self.max_halo = max(self.max_halo, h)
+        self.max_send = max(self.max_send, n_send)
 
     def _model_slot(self, ref):
-        if ref in self._value_slot:
-            return self._value_slot[ref]
+        s = self._value_slot.get(ref)
+        if s is not None:
+            return s
         return -1 - self._halo_of[ref]                        # halo row, fixed up in _fixup_wave
 
     def _end_level_wave(self, level: int, wave: Wave):
@@ -195,7 +307,10 @@ class DistributedSolver(BatchedSolver):
         return waves
 
     def _grow_pool(self, extra_slots: int):
-        self.ex._grow(extra_slots, halo_rows=self.max_halo, send_rows=self.max_send)
+        if self.transport == "push":
+            self.ex._grow(extra_slots)                        # inside the fixed symmetric allocation
+        else:
+            self.ex._grow(extra_slots, halo_rows=self.max_halo, send_rows=self.max_send)
 
     def _fixup_wave(self, w: Wave):
         """Halo references become rows after the pool (valid once the pool has its planned size)."""
@@ -205,13 +320,26 @@ class DistributedSolver(BatchedSolver):
             w.model_slots = [[s if s >= 0 else base + (-1 - s) for s in ms] for ms in w.model_slots]
         x = getattr(w, "xchg", None)
         if x and "send_idx" not in x:
-            x["send_idx"] = ex._dev_i32(x["send_slots"]) if x["send_slots"] else None
-            self.halo_bytes += sum(x["recv_counts"]) * ex.layout.P * 4
+            if self.transport == "push":
+                if x["send_slots"]:
+                    x["send_idx"], x["dst_dev"] = ex._upload(np.asarray(x["send_slots"], dtype=np.int32),
+                                                             np.asarray(x["dst_ptrs"], dtype=np.int64))
+                else:
+                    x["send_idx"] = None
+                self.halo_bytes += x["n_recv"] * ex.layout.P * 4
+            else:
+                x["send_idx"] = ex._dev_i32(x["send_slots"]) if x["send_slots"] else None
+                self.halo_bytes += sum(x["recv_counts"]) * ex.layout.P * 4
 
     # -- execution --------------------------------------------------------------------------
     def exchange(self, x: dict):
-        import torch.distributed as dist
         ex = self.ex
+        if self.transport == "push":
+            if x["send_idx"] is not None:
+                ex.push_rows(x["send_idx"], x["dst_dev"])
+            ex.symm_barrier()                                 # every rank, every exchange level
+            return
+        import torch.distributed as dist
         ld = ex.layout.ld
         n_send, n_recv = sum(x["send_counts"]), sum(x["recv_counts"])
         if n_send:

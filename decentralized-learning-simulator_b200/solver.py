@@ -13,7 +13,7 @@ CSR construction, minibatch index); `run()` then only launches.  Without a prior
 `run()` / `run_with_loss()` stream the graph: level k+1 is planned on the host while level k
 executes on the GPU, so only the first level's planning is exposed.
 """
-from collections import defaultdict
+from collections import Counter, defaultdict
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -86,8 +86,25 @@ class BatchedSolver:
 
     # -- planning ---------------------------------------------------------------------------
     def levelise(self) -> List[List[str]]:
-        """Kahn wavefronts: level(t) = 1 + max(level of inputs).  Source tasks are level 0
-        (`get_source_tasks`, dasklearn/tasks/dag.py:15-19)."""
+        """Wavefronts: level(t) = 1 + max(level of inputs); source tasks are level 0
+        (`get_source_tasks`, dasklearn/tasks/dag.py:15-19).  The serialized list of the reference is in creation
+        order, which is topological (a consumer names producers that already exist), so one pass in list order
+        settles every level; any other order falls back to Kahn's algorithm."""
+        level: Dict[str, int] = {}
+        get = level.__getitem__
+        try:
+            for n, t in self.tasks.items():
+                ins = t["inputs"]
+                level[n] = 1 + max(map(get, next(zip(*ins)))) if ins else 0
+        except KeyError:
+            return self._levelise_kahn()
+        self._level_of = level
+        levels: List[List[str]] = [[] for _ in range(max(level.values()) + 1)] if level else []
+        for n, l in level.items():
+            levels[l].append(n)
+        return levels
+
+    def _levelise_kahn(self) -> List[List[str]]:
         tasks = self.tasks
         indeg = {n: len(t["inputs"]) for n, t in tasks.items()}
         frontier = [n for n, d in indeg.items() if d == 0]
@@ -109,6 +126,7 @@ class BatchedSolver:
         if seen != len(self.tasks):
             raise RuntimeError("compute graph has a cycle or dangling inputs (%d of %d tasks reachable)"
                                % (seen, len(self.tasks)))
+        self._level_of = {n: li for li, names in enumerate(levels) for n in names}
         return levels
 
     def _plan_levels(self):
@@ -118,8 +136,8 @@ class BatchedSolver:
         ls = ex.settings.learning
         value_slot: Dict[Tuple[str, int], int] = {}
         sim_refs: Dict[int, int] = defaultdict(int)     # simulated reference counts during planning
-        for s_live in np.nonzero(ex.refs)[0]:
-            sim_refs[int(s_live)] = int(ex.refs[s_live])
+        live = np.nonzero(ex.refs)[0]
+        sim_refs.update(zip(live.tolist(), ex.refs[live].tolist()))
         free: List[int] = list(ex.free)
         self._planned_slots = ex.n_slots
         self._plan_free, self._plan_refs = free, sim_refs
@@ -162,6 +180,9 @@ class BatchedSolver:
             if ref in grad_slot:
                 pending.append(grad_slot[ref])
 
+        # single-GPU solve: every model reference is a pool slot (no halo rows) -> plain dictionary lookups
+        local_only = type(self)._model_slot is BatchedSolver._model_slot
+        model_slot = value_slot.__getitem__ if local_only else self._model_slot
         for li, names in enumerate(self.levelise()):
             by_func: Dict[str, Wave] = {}
             # a level may hold two train tasks of one node only in malformed graphs; detect in executor
@@ -209,16 +230,25 @@ class BatchedSolver:
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
                 elif func == "aggregate":
-                    refs = [tuple(m) for m in d["models"]]
-                    ms = [self._model_slot(m) for m in refs]
+                    refs = d["models"]
+                    try:
+                        ms = list(map(model_slot, refs))             # placeholders are tuples after pickle
+                    except TypeError:                                # lists (e.g. a JSON round trip)
+                        refs = [tuple(m) for m in refs]
+                        ms = list(map(model_slot, refs))
                     slot = take()
                     w.model_slots.append(ms)
-                    w.weights.append(list(d["weights"]) if d.get("weights") else None)
+                    wts = d.get("weights")
+                    w.weights.append(list(wts) if wts else None)
                     w.out_slots.append(slot)
                     sim_refs[slot] += keep
                     value_slot[(name, 0)] = slot
-                    pending_release.extend(x for x in ms if x >= 0)
-                    pending_release.extend(grad_slot[m] for m in refs if m in grad_slot)
+                    if local_only:
+                        pending_release.extend(ms)
+                    else:
+                        pending_release.extend([x for x in ms if x >= 0])
+                    if grad_slot:
+                        pending_release.extend([grad_slot[m] for m in map(tuple, refs) if m in grad_slot])
                 elif func == "compute_gradient":
                     # functions.py:80-82: forward/backward on the first minibatch, no optimizer step; the
                     # result is the UNCHANGED model (an alias of the input row) plus a gradient row
@@ -306,8 +336,8 @@ class BatchedSolver:
                 if n_cons == 0:
                     self.sink_slots[name] = value_slot[(name, 0)]
             # inputs are released only after the whole level ran (their rows are read by this level)
-            for s in pending_release:
-                n = sim_refs[s] - 1
+            for s, c in Counter(pending_release).items():      # one visit per distinct row, not per edge
+                n = sim_refs[s] - c
                 assert n >= 0
                 sim_refs[s] = n
                 if n == 0:

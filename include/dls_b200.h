@@ -101,6 +101,14 @@ int dls_copy_rows(const float *X, int64_t ldx, float *Y, int64_t ldy, const int3
 int dls_broadcast_row(const float *src, float *Y, int64_t ldy, const int32_t *dst_rows,
                       int32_t n_rows, int64_t P, void *stream);
 
+/* Multi-GPU halo push (replaces the broker-to-broker transfer of pickled models, dasklearn/broker.py:207-219):
+ * transfer e copies X[src_rows[e], 0:P) to the row that starts at device address dst_ptrs[e], which may be
+ * PEER memory mapped into this process (another GPU's halo rows).  Destinations must be 16-byte aligned and hold
+ * at least ceil(P/4)*4 floats.  The kernel ends with a system-scope fence; the caller must run a cross-GPU
+ * barrier on `stream` before any GPU reads the rows pushed to it.  At most 65535 transfers per call. */
+int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_rows, const uint64_t *dst_ptrs,
+                  int32_t n_transfers, int64_t P, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * train wave — replaces N calls of functions.train -> ModelTrainer.train
  * (dasklearn/functions.py:28-77, dasklearn/model_trainer.py:60-131) + torch.optim.SGD

@@ -335,6 +335,106 @@ agg_staged_uniform_kernel(const float *__restrict__ X, int64_t ldx, float *__res
     cp_async_wait<0>();
 }
 
+// ------------------------------------------------------------------------------------------
+// Staged variant for a uniform fan-in AND one weight for the whole wave (a D-PSGD aggregate wave without
+// `weights`: every entry is float(1 / (k+1)), fedavg.py:14-15).  The CSR shrinks to 16-bit source indices
+// (FAN rounded up to 8 per row), which is what lets 1024 source rows x fan-in 11 fit next to three stages.
+// Same arithmetic: acc = x_first * 0; acc = fadd_rn(acc, fmul_rn(w, x)) in list order.
+// ------------------------------------------------------------------------------------------
+template <int TW4, int FAN>
+__global__ void __launch_bounds__(STG_THREADS, 1)
+agg_staged_u16_kernel(const float *__restrict__ X, int64_t ldx, float *__restrict__ Y, int64_t ldy,
+                      const int32_t *__restrict__ colidx, const float *__restrict__ wval,
+                      const int32_t *__restrict__ src_rows, const int32_t *__restrict__ out_rows,
+                      int n_rows, int n_src, int64_t P4, int n_tiles, int n_stages)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int stage_bytes = n_src * TW4 * 16;
+    const float w = __ldg(wval);                                 // the wave's one weight
+    unsigned char *stages = smem_raw;
+    uint16_t *s_idx = reinterpret_cast<uint16_t *>(smem_raw + (size_t)n_stages * stage_bytes);
+    constexpr int ROWS_PER_PASS = STG_THREADS / TW4;
+    constexpr int MAX_CP = 8;
+    constexpr int FANP = (FAN + 7) & ~7;                         // 16-bit entries per row, 16-byte groups
+    const int lane_c = threadIdx.x % TW4;
+    const int rsub = threadIdx.x / TW4;
+    for (int i = threadIdx.x; i < n_rows * FANP; i += STG_THREADS) {
+        const int r = i / FANP, q = i - r * FANP;
+        s_idx[i] = q < FAN ? (uint16_t)colidx[r * FAN + q] : (uint16_t)0;
+    }
+    const float *cp_src[MAX_CP];
+    const int n_cp = (n_src * TW4 + STG_THREADS - 1) / STG_THREADS;
+#pragma unroll
+    for (int k = 0; k < MAX_CP; ++k) {
+        const int r = rsub + k * ROWS_PER_PASS;
+        const int64_t xr = (r < n_src) ? (src_rows ? (int64_t)__ldg(src_rows + r) : (int64_t)r) : 0;
+        cp_src[k] = X + xr * ldx + 4 * lane_c;
+    }
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(stages);
+
+    auto issue = [&](int tile, int stage) {
+        if (tile < n_tiles) {
+            const int64_t c0 = (int64_t)tile * TW4;
+            if (c0 + lane_c < P4) {
+                const uint32_t dst = smem_base + (uint32_t)stage * stage_bytes + threadIdx.x * 16;
+#pragma unroll
+                for (int k = 0; k < MAX_CP; ++k)
+                    if (k < n_cp && rsub + k * ROWS_PER_PASS < n_src)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                                     :: "r"(dst + k * (STG_THREADS * 16)), "l"(cp_src[k] + 4 * c0));
+            }
+        }
+        cp_async_commit();
+    };
+
+    const int first = blockIdx.x;
+    for (int s = 0; s < n_stages - 1; ++s) issue(first + s * gridDim.x, s);
+    int it = 0, cur = 0;
+    for (int tile = first; tile < n_tiles; tile += gridDim.x, ++it) {
+        switch (n_stages) {
+            case 2: cp_async_wait<0>(); break;
+            case 3: cp_async_wait<1>(); break;
+            case 4: cp_async_wait<2>(); break;
+            case 5: cp_async_wait<3>(); break;
+            case 6: cp_async_wait<4>(); break;
+            case 7: cp_async_wait<5>(); break;
+            default: cp_async_wait<6>(); break;
+        }
+        __syncthreads();
+        int nxt = cur - 1;
+        if (nxt < 0) nxt = n_stages - 1;
+        issue(tile + (n_stages - 1) * gridDim.x, nxt);
+        const unsigned char *src = stages + (size_t)cur * stage_bytes + lane_c * 16;
+        const int64_t c = (int64_t)tile * TW4 + lane_c;
+        for (int r = rsub; r < n_rows; r += ROWS_PER_PASS) {
+            const uint4 *er = reinterpret_cast<const uint4 *>(s_idx + r * FANP);
+            uint32_t pk[FANP / 2];
+#pragma unroll
+            for (int q = 0; q < FANP / 8; ++q) {
+                const uint4 pr = er[q];
+                pk[4 * q] = pr.x; pk[4 * q + 1] = pr.y; pk[4 * q + 2] = pr.z; pk[4 * q + 3] = pr.w;
+            }
+            float4 xv[FAN];
+#pragma unroll
+            for (int q = 0; q < FAN; ++q) {
+                const uint32_t idx = (q & 1) ? (pk[q >> 1] >> 16) : (pk[q >> 1] & 0xffffu);
+                xv[q] = *reinterpret_cast<const float4 *>(src + idx * (TW4 * 16));
+            }
+            float4 acc;
+            acc.x = __fmul_rn(xv[0].x, 0.f); acc.y = __fmul_rn(xv[0].y, 0.f);
+            acc.z = __fmul_rn(xv[0].z, 0.f); acc.w = __fmul_rn(xv[0].w, 0.f);
+#pragma unroll
+            for (int q = 0; q < FAN; ++q) acc_term(acc, w, xv[q]);
+            if (c < P4) {
+                const int64_t orow = out_rows ? __ldg(out_rows + r) : r;
+                *reinterpret_cast<float4 *>(Y + orow * ldy + 4 * c) = acc;
+            }
+        }
+        if (++cur == n_stages) cur = 0;
+    }
+    cp_async_wait<0>();
+}
+
 // CSR entries in global memory for waves whose CSR does not fit in shared memory next to the stages.
 template <int TW4>
 __global__ void agg_pack_entries_kernel(const int32_t *__restrict__ colidx, const float *__restrict__ wval,
@@ -380,12 +480,14 @@ copy_rows_kernel(const float *__restrict__ X, int64_t ldx, float *__restrict__ Y
 struct StagedPlan { int tw4; int stages; bool csr_smem; size_t smem; int sms; };
 
 // Largest tile width that still leaves >= 3 stages (2 loads in flight while one tile is consumed).
-static bool plan_staged(const DeviceInfo &di, int n_rows, int n_src, int n_ent, StagedPlan &pl)
+static bool plan_staged(const DeviceInfo &di, int n_rows, int n_src, int n_ent, StagedPlan &pl, int u16_fan = 0)
 {
     pl.sms = di.sms;
     const int64_t budget = di.smem_optin - 256;
-    const int64_t rowptr_bytes = (int64_t)((n_rows + 1 + 3) & ~3) * 4;
-    const int64_t csr_bytes = ((int64_t)n_ent + n_rows) * 8;   // room for the uniform kernel's pair padding
+    // u16_fan > 0: the uniform-weight kernel (16-bit indices, fan-in padded to 8, no row pointers)
+    const int64_t rowptr_bytes = u16_fan ? 0 : (int64_t)((n_rows + 1 + 3) & ~3) * 4;
+    const int64_t csr_bytes = u16_fan ? (int64_t)n_rows * ((u16_fan + 7) & ~7) * 2
+                                      : ((int64_t)n_ent + n_rows) * 8;   // room for the uniform kernel's pair padding
     const int e_tw = tune_value(TUNE_AGG_TW4), e_st = tune_value(TUNE_AGG_STAGES);   // dls_tune() overrides (0 = auto)
     const int cand[3] = {16, 8, 4};
     for (int pass = 0; pass < 2; ++pass) {
@@ -463,6 +565,50 @@ static int launch_uniform_fan(int fan, const StagedPlan &pl, const float *X, int
     }
 }
 
+template <int TW4, int FAN>
+static int launch_u16_t(const StagedPlan &pl, const float *X, int64_t ldx, float *Y, int64_t ldy,
+                        const int32_t *colidx, const float *w, const int32_t *src_rows, const int32_t *out_rows, int n_rows,
+                        int n_src, int64_t P4, cudaStream_t st)
+{
+    if ((n_src * TW4 + STG_THREADS - 1) / STG_THREADS > 8) return DLS_E_SHAPE;
+    cudaError_t e = cudaFuncSetAttribute(agg_staged_u16_kernel<TW4, FAN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+    if (e != cudaSuccess) return (int)e;
+    const int n_tiles = (int)((P4 + TW4 - 1) / TW4);
+    const int rounds = (n_tiles + pl.sms - 1) / pl.sms;
+    const int grid = (n_tiles + rounds - 1) / rounds;
+    agg_staged_u16_kernel<TW4, FAN><<<grid, STG_THREADS, pl.smem, st>>>(
+        X, ldx, Y, ldy, colidx, w, src_rows, out_rows, n_rows, n_src, P4, n_tiles, pl.stages);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int TW4>
+static int launch_u16_fan(int fan, const StagedPlan &pl, const float *X, int64_t ldx, float *Y, int64_t ldy,
+                          const int32_t *colidx, const float *w, const int32_t *src_rows, const int32_t *out_rows,
+                          int n_rows, int n_src, int64_t P4, cudaStream_t st)
+{
+    switch (fan) {
+#define DLS_FAN_CASE(F) \
+    case F: return launch_u16_t<TW4, F>(pl, X, ldx, Y, ldy, colidx, w, src_rows, out_rows, n_rows, n_src, P4, st);
+        DLS_FAN_CASE(2) DLS_FAN_CASE(3) DLS_FAN_CASE(4) DLS_FAN_CASE(5) DLS_FAN_CASE(6) DLS_FAN_CASE(7)
+        DLS_FAN_CASE(8) DLS_FAN_CASE(9) DLS_FAN_CASE(10) DLS_FAN_CASE(11) DLS_FAN_CASE(12) DLS_FAN_CASE(13)
+        DLS_FAN_CASE(14) DLS_FAN_CASE(15) DLS_FAN_CASE(16)
+#undef DLS_FAN_CASE
+        default: return DLS_E_SHAPE;
+    }
+}
+
+static int launch_u16(int fan, const StagedPlan &pl, const float *X, int64_t ldx, float *Y, int64_t ldy,
+                      const int32_t *colidx, const float *w, const int32_t *src_rows, const int32_t *out_rows, int n_rows,
+                      int n_src, int64_t P4, cudaStream_t st)
+{
+    if (pl.tw4 == 16) return launch_u16_fan<16>(fan, pl, X, ldx, Y, ldy, colidx, w, src_rows, out_rows, n_rows, n_src, P4, st);
+    if (pl.tw4 == 8) return launch_u16_fan<8>(fan, pl, X, ldx, Y, ldy, colidx, w, src_rows, out_rows, n_rows, n_src, P4, st);
+    if (pl.tw4 == 4) return launch_u16_fan<4>(fan, pl, X, ldx, Y, ldy, colidx, w, src_rows, out_rows, n_rows, n_src, P4, st);
+    return DLS_E_SHAPE;
+}
+
 static int launch_uniform(int fan, const StagedPlan &pl, const float *X, int64_t ldx, float *Y, int64_t ldy,
                           const int32_t *colidx, const float *wval, const int32_t *src_rows,
                           const int32_t *out_rows, int n_rows, int n_src, int64_t P4, cudaStream_t st)
@@ -524,6 +670,13 @@ extern "C" int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t l
     const int n_ent = nnz;
     if (n_src_rows > 0 && n_src_rows <= 65535 && nnz >= 0 && (variant == 2 || variant == 3 || variant == 0))
         can_stage = plan_staged(*di, n_rows, n_src_rows, n_ent, pl) && pl.csr_smem;
+    if (variant == 4) {
+        // the caller asserts a uniform fan-in AND that every entry carries the weight wval[0]
+        if (n_src_rows <= 0 || n_src_rows > 65535 || nnz % n_rows != 0) return DLS_E_SHAPE;
+        const int fan = nnz / n_rows;
+        if (fan < 2 || fan > 16 || !plan_staged(*di, n_rows, n_src_rows, n_ent, pl, fan) || !pl.csr_smem) return DLS_E_SHAPE;
+        return launch_u16(fan, pl, X, ldx, Y, ldy, colidx, wval, src_rows, out_rows, n_rows, n_src_rows, P4, st);
+    }
     if (variant == 3) {
         // the caller asserts a uniform fan-in: rowptr[r] == r * (nnz / n_rows)
         if (!can_stage || nnz % n_rows != 0) return DLS_E_SHAPE;
@@ -551,13 +704,20 @@ extern "C" int dls_agg_variant_fits(int32_t variant, int32_t n_rows, int32_t n_s
 {
     if (n_rows < 0 || n_src_rows < 0 || nnz < 0) return DLS_E_ARG;
     if (variant == 0 || variant == 1) return 1;
-    if (variant != 2 && variant != 3) return DLS_E_ARG;
+    if (variant != 2 && variant != 3 && variant != 4) return DLS_E_ARG;
     if (n_rows == 0) return 1;
     const DeviceInfo *di = nullptr;
     int rc = device_info(&di);
     if (rc) return rc < 0 ? rc : -rc;
     StagedPlan pl;
     if (n_src_rows <= 0 || n_src_rows > 65535) return 0;
+    if (variant == 4) {
+        if (nnz % n_rows != 0) return 0;
+        const int fan = nnz / n_rows;
+        if (fan < 2 || fan > 16) return 0;
+        if (!plan_staged(*di, n_rows, n_src_rows, nnz, pl, fan) || !pl.csr_smem) return 0;
+        return (n_src_rows * pl.tw4 + STG_THREADS - 1) / STG_THREADS > 8 ? 0 : 1;
+    }
     if (!(plan_staged(*di, n_rows, n_src_rows, nnz, pl) && pl.csr_smem)) return 0;
     if (variant == 3) {
         if (nnz % n_rows != 0) return 0;

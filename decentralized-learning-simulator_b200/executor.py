@@ -302,14 +302,15 @@ class WaveExecutor:
         if np.intersect1d(src_rows64, outs).size:
             raise DlsError("aggregate wave would overwrite one of its own inputs")
         uniform = n_rows > 0 and int(lens.min()) == int(lens.max()) and 2 <= int(lens[0]) <= 16
-        # shared-memory staged kernels when the wave fits (uniform fan-in -> the specialised one), else the
+        one_weight = uniform and (weights is None or not any(weights))
+        # shared-memory staged kernels when the wave fits (uniform fan-in -> the specialised ones), else the
         # L2 gather kernel: asked of the library (dls_agg_variant_fits), no trial launches
-        hint = {"variant": self._agg_variant(n_rows, int(src_rows64.size), nnz, uniform)}
+        hint = {"variant": self._agg_variant(n_rows, int(src_rows64.size), nnz, uniform, one_weight)}
         up = self._upload(rowptr, col.astype(np.int32), wv.astype(np.float32), src_rows64.astype(np.int32), outs)
         return (*up, int(src_rows64.size), hint)
 
-    def _agg_variant(self, n_rows: int, n_src: int, nnz: int, uniform: bool) -> int:
-        for v in ((3, 2) if uniform else (2,)):
+    def _agg_variant(self, n_rows: int, n_src: int, nnz: int, uniform: bool, one_weight: bool = False) -> int:
+        for v in ((4, 3, 2) if one_weight else (3, 2) if uniform else (2,)):
             if K.agg_variant_fits(v, n_rows, n_src, nnz):
                 return v
         return 1

@@ -62,14 +62,16 @@ int         dls_tune(int32_t key, int32_t value);
  * rowptr[n_rows], the number of (colidx, wval) entries.  X and Y may be
  * the same allocation as long as no output row is also an input row of the same call.
  * `variant`: 0 = auto (gather), 1 = gather through L2, 2 = shared-memory staged column tiles,
- * 3 = staged + the caller asserts a uniform fan-in F = nnz / n_rows in [2, 16] (rowptr[r] == r*F).
- * 2 and 3 return DLS_E_SHAPE when the wave's source rows / CSR do not fit in shared memory.
+ * 3 = staged + the caller asserts a uniform fan-in F = nnz / n_rows in [2, 16] (rowptr[r] == r*F),
+ * 4 = like 3 and the caller also asserts that every entry carries the weight wval[0] (a D-PSGD wave without
+ * explicit weights): the CSR is kept as 16-bit indices, so larger waves fit (1024 source rows x fan-in 11).
+ * 2, 3 and 4 return DLS_E_SHAPE when the wave's source rows / CSR do not fit in shared memory.
  * ------------------------------------------------------------------------------------------ */
 int dls_agg_spmm_f32(const float *X, int64_t ldx, float *Y, int64_t ldy,
                      const int32_t *rowptr, const int32_t *colidx, const float *wval,
                      const int32_t *src_rows, const int32_t *out_rows, int32_t n_rows,
                      int32_t n_src_rows, int32_t nnz, int64_t P, int32_t variant, void *stream);
-/* 1 if `variant` (2 or 3) accepts a wave of this shape on the current device, 0 if not (variant 1 always
+/* 1 if `variant` (2, 3 or 4) accepts a wave of this shape on the current device, 0 if not (variant 1 always
  * does), negative on bad arguments: lets the caller choose a variant without a trial launch. */
 int dls_agg_variant_fits(int32_t variant, int32_t n_rows, int32_t n_src_rows, int32_t nnz);
 

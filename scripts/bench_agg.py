@@ -23,7 +23,7 @@ from dls_b200.layout import GNLENET as L
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--nodes", type=int, nargs="+", default=[256, 1024])
-    ap.add_argument("--variants", type=int, nargs="+", default=[1, 2])
+    ap.add_argument("--variants", type=int, nargs="+", default=[1, 3, 4])
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="sweep staged tile width / stage count (tuning)")

@@ -34,7 +34,7 @@ class OracleExecutor(WaveExecutor):
         """CPU stand-in of WaveExecutor._upload (the product one stages through pinned memory to a CUDA device)."""
         return [torch.from_numpy(np.ascontiguousarray(a).copy()) for a in arrays]
 
-    def _agg_variant(self, n_rows, n_src, nnz, uniform):
+    def _agg_variant(self, n_rows, n_src, nnz, uniform, one_weight=False):
         return 1
 
     def init_rows(self, slots):

@@ -37,10 +37,12 @@ def _run(cuda, X, rowptr, col, w, P, variant, src_rows=None, out_rows=None, n_ou
     return Yd.cpu().numpy()
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("tag,fan,weighted", [("f5", 5, False), ("f11", 11, False), ("f2w", 2, True), ("f5w", 5, True)])
 def test_golden_fedavg(cuda, golden_dir, variant, tag, fan, weighted):
     """Same inputs as the reference-generated fixture: CUDA result == reference bits."""
+    if variant == 4 and weighted:
+        pytest.skip("variant 4 is for waves with one weight")
     g = np.load(os.path.join(golden_dir, "fedavg_kat.npz"))
     X = np.zeros((fan, L.ld), np.float32)
     X[:, :L.P] = kat_rows(fan, L.P, salt=fan + (100 if weighted else 0))
@@ -50,7 +52,7 @@ def test_golden_fedavg(cuda, golden_dir, variant, tag, fan, weighted):
     assert np.array_equal(Y[0, :L.P].view(np.uint32), g[tag + "_y"].view(np.uint32))
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("n,k", [(16, 4), (64, 6), (200, 7)])
 def test_wave_vs_oracle(cuda, variant, n, k):
     """A whole D-PSGD aggregate wave on a k-regular topology, shuffled arrival order, own model last."""
@@ -147,3 +149,28 @@ def test_copy_and_broadcast_rows(cuda):
     assert torch.equal(Y[0, :L.P], X[3, :L.P]) and torch.equal(Y[7, :L.P], X[1, :L.P])
     K.broadcast_row(X[5], Y, torch.arange(8, dtype=torch.int32, device=cuda), L.P)
     assert torch.equal(Y[:, :L.P], X[5, :L.P].expand(8, L.P))
+
+
+def test_metric_size_wave_all_variants_agree(cuda):
+    """The metric's shape — 1024 nodes, 10-regular, fan-in 11, no explicit weights: the 16-bit-index staged kernel
+    (variant 4, the one the executor picks there) gives the bits of the gather kernel, which the oracle checks at
+    smaller sizes; 8 sampled rows are also compared with the oracle directly."""
+    n, k = 1024, 10
+    nb = synthetic.kreg_topology(n, k, seed=42)
+    lists = [list(nb[i]) + [i] for i in range(n)]
+    rowptr, col, w = _csr(lists)
+    rs = np.random.RandomState(0)
+    X = torch.from_numpy((rs.standard_normal((n, L.ld)) * np.exp2(rs.randint(-6, 6, (n, 1)))).astype(np.float32)).to(cuda)
+    outs = {}
+    for v in (1, 4):
+        assert K.agg_variant_fits(v, n, n, len(col))
+        Y = torch.full((n, L.ld), float("nan"), device=cuda)
+        K.agg_spmm(X, Y, torch.from_numpy(rowptr).to(cuda), torch.from_numpy(col).to(cuda),
+                   torch.from_numpy(w).to(cuda), L.P, n_src_rows=n, variant=v)
+        torch.cuda.synchronize()
+        outs[v] = Y[:, :L.P]
+    assert torch.equal(outs[1].view(torch.int32), outs[4].view(torch.int32))
+    Xh = X.cpu().numpy()
+    for r in range(0, n, 128):
+        want = O.fedavg_numpy([Xh[s, :L.P] for s in lists[r]])
+        assert np.array_equal(outs[4][r].cpu().numpy().view(np.uint32), want.view(np.uint32))

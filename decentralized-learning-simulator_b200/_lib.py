@@ -45,6 +45,7 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_int64, c_void_p]),
     "dls_tc_probe": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_void_p, c_int32, ctypes.c_uint32,
                              c_int32, c_void_p, c_int32, c_void_p, c_void_p]),
+    "dls_tc_contention": (c_int, [c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
     "dls_eval_wave_noalloc": (c_int, [c_int32, c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p, c_int32,
                                       c_void_p, c_void_p, c_void_p]),
 }

@@ -9,6 +9,7 @@
 // reduction uses a fixed order (no float atomics), so results are run-to-run deterministic.
 #include "gnlenet.cuh"
 #include "conv_simt.cuh"
+#include "tc_common.cuh"
 #include <math.h>
 
 namespace dls {
@@ -45,6 +46,16 @@ int64_t carve(Workspace &ws, void *base, int n_groups, int gs, int n_models, boo
     ws.desc_i32 = c.take<int32_t>(S + 2 * (int64_t)n_groups + 16);
     ws.precision = precision;
     ws.prep_tc = precision == 1 ? (void *)c.take<uint16_t>((int64_t)n_models * TC_PREP_ELEMS) : nullptr;
+    ws.a1p = ws.a2p = ws.dc2p = ws.dc3p = ws.zplane = nullptr;
+    if (precision == 1) {
+        ws.zplane = c.take<uint16_t>(RUNP15 * 8);
+        ws.a1p = c.take<uint16_t>(S * A1P_SZ);
+        ws.a2p = c.take<uint16_t>(S * A2P_SZ);
+        if (backward) {
+            ws.dc2p = c.take<uint16_t>(S * DC2P_SZ);
+            ws.dc3p = c.take<uint16_t>(S * DC3P_SZ);
+        }
+    }
     ws.p1 = ws.st1 = ws.st2 = ws.st3 = nullptr;
     ws.idx1 = ws.idx2 = ws.idx3 = nullptr;
     ws.da3 = ws.dc3 = ws.da2 = ws.dc2 = ws.da1 = ws.dp1 = ws.gnp = nullptr;
@@ -234,10 +245,12 @@ conv1_pool_gn_relu_kernel(Pass p, Workspace ws, int save_bwd)
 template <int C, int H, int PH>
 __global__ void __launch_bounds__(256)
 gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, float *__restrict__ stats,
-                    uint8_t *__restrict__ idx, Pass p, int gw_off, int gb_off, int save_bwd)
+                    uint8_t *__restrict__ idx, Pass p, int gw_off, int gb_off, int save_bwd, int cbias_off,
+                    uint16_t *__restrict__ planes)
 {
     constexpr int SZ = H * H * C;
     __shared__ __align__(16) float cs[SZ];
+    __shared__ __align__(16) float ps[PH == 7 ? PH * PH * C : 4];   // pooled output, staged for the bf16 plane stores
     __shared__ float red[64];
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
@@ -252,10 +265,16 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
     constexpr int N4 = SZ / 4, NE4 = (N4 + 255) / 256;
     const int c0 = (4 * t) % C, grp = c0 >= (C / 2);              // 1024 % C == 0: fixed channels per thread
     float4 v[NE4];
+    // cbias_off >= 0: `cpre` is the convolution without its bias (tensor-core path); it is added here
+    const float4 cb = cbias_off >= 0 ? *reinterpret_cast<const float4 *>(row + cbias_off + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int k = 0; k < NE4; ++k) {
         const int e4 = t + k * 256;
-        v[k] = e4 < N4 ? __ldg(reinterpret_cast<const float4 *>(src) + e4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e4 < N4) {
+            const float4 x = __ldg(reinterpret_cast<const float4 *>(src) + e4);
+            v[k] = make_float4(x.x + cb.x, x.y + cb.y, x.z + cb.z, x.w + cb.w);
+        }
     }
     float s = 0.f;
 #pragma unroll
@@ -303,7 +322,25 @@ gn_pool_relu_kernel(const float *__restrict__ cpre, float *__restrict__ aout, fl
                 if (v > best) { best = v; bi = dy * 3 + dx; }
             }
         dst[o] = best > 0.f ? best : 0.f;
+        if (PH == 7) ps[o] = best > 0.f ? best : 0.f;
         if (save_bwd) idx[(int64_t)slot * (PH * PH * C) + o] = (uint8_t)bi;
+    }
+    if (PH == 7 && planes) {
+        // the block output also leaves as bf16 channel-chunk planes [C/8][RUNP7][8] (what conv3 forward and the conv3
+        // weight gradient stage with bulk copies): entry r = py * 9 + px; the two gap pixels after a row are zero
+        __syncthreads();
+        uint4 *pl = reinterpret_cast<uint4 *>(planes + (int64_t)slot * (C / 8) * RUNP7 * 8);
+        for (int e = t; e < PH * PH * (C / 8); e += 256) {
+            const int c8 = e % (C / 8), pp = e / (C / 8), py = pp / PH, px = pp - py * PH;
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = ps[pp * C + c8 * 8 + k];
+            pl[c8 * RUNP7 + py * (PH + 2) + px] = tc::pack8_bf16(o);
+        }
+        for (int e = t; e < (PH - 1) * 2 * (C / 8); e += 256) {
+            const int c8 = e % (C / 8), gq = e / (C / 8), py = gq >> 1;
+            pl[c8 * RUNP7 + py * (PH + 2) + PH + (gq & 1)] = make_uint4(0u, 0u, 0u, 0u);
+        }
     }
     if (save_bwd && t == 0) {
         float *st = stats + (int64_t)slot * 4;
@@ -441,10 +478,11 @@ __global__ void __launch_bounds__(256, (POOL && H == 15) ? 6 : 4)
 gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout,
                     const uint8_t *__restrict__ idx, const float *__restrict__ cpre,
                     const float *__restrict__ stats, float *__restrict__ dc, float *__restrict__ gnp,
-                    Pass p, int gw_off, int gnp_off)
+                    Pass p, int gw_off, int gnp_off, int cbias_off, uint16_t *__restrict__ planes)
 {
     constexpr int SZ = H * H * C;
     constexpr int OSZ = POOL ? PH * PH * C : SZ;
+    constexpr int RUNP = H == 15 ? RUNP15 : RUNP7;
     __shared__ float dg[SZ];
     __shared__ float red[32];
     const int slot = blockIdx.x, t = threadIdx.x;
@@ -459,6 +497,7 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     const int ch = t % C, grp = ch >= (C / 2);
     const float mean = st[grp * 2], rstd = st[grp * 2 + 1];
     const float gam = row[gw_off + ch];
+    const float cb = cbias_off >= 0 ? row[cbias_off + ch] : 0.f;    // `cpre` without the conv bias (tensor-core path)
 
     if (POOL) {
         // route each pooled gradient to the arg-max position of its 3x3/2 window.  Windows of one colour
@@ -494,7 +533,7 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
         const int e = t + k * 256;
         if (KEEP) xh[k] = 0.f;
         if (e < SZ) {
-            const float xhat = (cp[e] - mean) * rstd;
+            const float xhat = ((cp[e] + cb) - mean) * rstd;
             const float d = POOL ? dg[e] : ((xhat * gam + bet) > 0.f ? das[e] : 0.f);
             if (KEEP) xh[k] = xhat;
             if (!POOL) dg[e] = d;                          // own element: no barrier needed before the second pass
@@ -521,10 +560,29 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     for (int k = 0; k < NE; ++k) {
         const int e = t + k * 256;
         if (e < SZ) {
-            const float xhat = KEEP ? xh[k] : (cp[e] - mean) * rstd;
+            const float xhat = KEEP ? xh[k] : ((cp[e] + cb) - mean) * rstd;
             const float v = rstd * (dg[e] * gam - m1 - xhat * m2);
-            dst[e] = v;
+            if (planes) dg[e] = v;                         // own element: staged for the plane stores below
+            else dst[e] = v;
             dbias += v;
+        }
+    }
+    if (POOL && planes) {
+        // precision 1: the gradient w.r.t. the conv output leaves ONLY as bf16 channel-chunk planes [C/8][RUNP][8]
+        // (entry r = y * (H + 2) + x, gap pixels zero): both its consumers, the data-gradient and the weight-gradient
+        // convolutions, stage it with bulk copies
+        __syncthreads();
+        uint4 *pl = reinterpret_cast<uint4 *>(planes + (int64_t)slot * (C / 8) * RUNP * 8);
+        for (int e = t; e < H * H * (C / 8); e += 256) {
+            const int c8 = e % (C / 8), pix = e / (C / 8), y = pix / H, x = pix - y * H;
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = dg[pix * C + c8 * 8 + k];
+            pl[c8 * RUNP + y * (H + 2) + x] = tc::pack8_bf16(o);
+        }
+        for (int e = t; e < (H - 1) * 2 * (C / 8); e += 256) {
+            const int c8 = e % (C / 8), gq = e / (C / 8), y = gq >> 1;
+            pl[c8 * RUNP + y * (H + 2) + H + (gq & 1)] = make_uint4(0u, 0u, 0u, 0u);
         }
     }
     // per-channel parameter-gradient partials of this sample: combine the 256/C threads of a channel
@@ -675,6 +733,8 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     if (rc) return rc;
     const int S = p.n_groups * p.gs;
     const int sv = save ? 1 : 0;
+    // the grouped tensor-core convolutions leave the conv bias to the GroupNorm kernels
+    const bool nobias = ws.precision == 1 && !tune_value(TUNE_CONV_UNGROUPED);
     if (ws.precision == 1) {
         if ((rc = conv1_fwd_tc(p, ws, save, st))) return rc;
     } else {
@@ -687,7 +747,7 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
         conv5_kernel<32, 32, 15, true><<<S, 256, 19 * 19 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PREP_STRIDE, PO_W2T, OFF_B2);
         DLS_LAUNCH_CHECK();
     }
-    gn_pool_relu_kernel<32, 15, 7><<<S, 256, 0, st>>>(ws.c2, ws.a2, ws.st2, ws.idx2, p, OFF_G2W, OFF_G2B, sv);
+    gn_pool_relu_kernel<32, 15, 7><<<S, 256, 0, st>>>(ws.c2, ws.a2, ws.st2, ws.idx2, p, OFF_G2W, OFF_G2B, sv, nobias ? OFF_B2 : -1, nobias ? ws.a2p : nullptr);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv3_fwd_tc(p, ws, st))) return rc;
@@ -695,7 +755,7 @@ int forward(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
         conv5_kernel<32, 64, 7, true><<<S, 256, 11 * 11 * 32 * 4, st>>>(ws.a2, ws.c3, p, ws.prep, PREP_STRIDE, PO_W3T, OFF_B3);
         DLS_LAUNCH_CHECK();
     }
-    gn_pool_relu_kernel<64, 7, 3><<<S, 256, 0, st>>>(ws.c3, ws.a3, ws.st3, ws.idx3, p, OFF_G3W, OFF_G3B, sv);
+    gn_pool_relu_kernel<64, 7, 3><<<S, 256, 0, st>>>(ws.c3, ws.a3, ws.st3, ws.idx3, p, OFF_G3W, OFF_G3B, sv, nobias ? OFF_B3 : -1, nullptr);
     DLS_LAUNCH_CHECK();
     return 0;
 }
@@ -741,22 +801,23 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane)
     if (ws.precision == 1) {
         SideStream *ss = nullptr;
         if ((rc = side_stream(&ss, 2 * lane))) return rc;
+        const bool nobias = !tune_value(TUNE_CONV_UNGROUPED);     // conv outputs carry no bias (conv_tc3_kernel)
         gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
-                                                              ws.gnp, p, OFF_G3W, 192);
+                                                              ws.gnp, p, OFF_G3W, 192, nobias ? OFF_B3 : -1, nobias ? ws.dc3p : nullptr);
         DLS_LAUNCH_CHECK();
         DLS_CUDA(cudaEventRecord(ss->fork, st));
         DLS_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
         if ((rc = conv3_wgrad_tc(p, ws, ss->s))) return rc;
         if ((rc = conv3_dgrad_tc(p, ws, st))) return rc;
         gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
-                                                               ws.gnp, p, OFF_G2W, 96);
+                                                               ws.gnp, p, OFF_G2W, 96, nobias ? OFF_B2 : -1, nobias ? ws.dc2p : nullptr);
         DLS_LAUNCH_CHECK();
         DLS_CUDA(cudaEventRecord(ss->fork, st));
         DLS_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
         if ((rc = conv2_wgrad_tc(p, ws, ss->s))) return rc;
         if ((rc = conv2_dgrad_tc(p, ws, st))) return rc;
         gn_block_bwd_kernel<32, 15, 15, false><<<S, 256, 0, st>>>(ws.da1, ws.a1, nullptr, ws.p1, ws.st1, ws.dp1,
-                                                                 ws.gnp, p, OFF_G1W, 0);
+                                                                 ws.gnp, p, OFF_G1W, 0, -1, nullptr);
         DLS_LAUNCH_CHECK();
         if ((rc = conv1_wgrad_tc(p, ws, st))) return rc;
         gn_param_reduce_kernel<<<p.n_groups, GNP_SZ, 0, st>>>(p, ws);
@@ -767,7 +828,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane)
     }
     // block 3
     gn_block_bwd_kernel<64, 7, 3, true><<<S, 256, 0, st>>>(ws.da3, ws.a3, ws.idx3, ws.c3, ws.st3, ws.dc3,
-                                                          ws.gnp, p, OFF_G3W, 192);
+                                                          ws.gnp, p, OFF_G3W, 192, -1, nullptr);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv3_wgrad_tc(p, ws, st))) return rc;
@@ -784,7 +845,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane)
     }
     // block 2
     gn_block_bwd_kernel<32, 15, 7, true><<<S, 256, 0, st>>>(ws.da2, ws.a2, ws.idx2, ws.c2, ws.st2, ws.dc2,
-                                                           ws.gnp, p, OFF_G2W, 96);
+                                                           ws.gnp, p, OFF_G2W, 96, -1, nullptr);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv2_wgrad_tc(p, ws, st))) return rc;
@@ -801,7 +862,7 @@ int backward(const Pass &p, Workspace &ws, cudaStream_t st, int lane)
     }
     // block 1 (GroupNorm -> ReLU after the pool), then the sparse conv1 weight gradient
     gn_block_bwd_kernel<32, 15, 15, false><<<S, 256, 0, st>>>(ws.da1, ws.a1, nullptr, ws.p1, ws.st1, ws.dp1,
-                                                             ws.gnp, p, OFF_G1W, 0);
+                                                             ws.gnp, p, OFF_G1W, 0, -1, nullptr);
     DLS_LAUNCH_CHECK();
     if (ws.precision == 1) {
         if ((rc = conv1_wgrad_tc(p, ws, st))) return rc;

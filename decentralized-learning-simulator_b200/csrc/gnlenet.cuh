@@ -27,6 +27,11 @@ constexpr int C3_SZ = H3 * H3 * C3;     // 3136
 constexpr int A3_SZ = PH3 * PH3 * C3;   // 576
 constexpr int GNP_SZ = 3 * (C1 + C2 + C3);   // per-slot partials: GN gamma, GN beta, conv bias gradient (384)
 
+// bf16 plane runs (tensor-core path): RUN = (H-1)*(H+2) + H pixels, padded to a multiple of 8
+constexpr int RUN15 = 14 * 17 + 15, RUNP15 = 256;     // 15x15 maps (a1, dc2): 253 pixels, plane = 4096 B
+constexpr int RUN7 = 6 * 9 + 7, RUNP7 = 64;           // 7x7 maps (a2, dc3): 61 pixels, plane = 1024 B
+constexpr int A1P_SZ = 4 * RUNP15 * 8, A2P_SZ = 4 * RUNP7 * 8, DC2P_SZ = 4 * RUNP15 * 8, DC3P_SZ = 8 * RUNP7 * 8;   // bf16 elements per sample
+
 constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
 constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200 + 2560;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)
 constexpr int PREP_SZ = 2 * W2T_SZ + 2 * W3T_SZ;   // W2t, W2d, W3t, W3d per model
@@ -43,6 +48,10 @@ struct Workspace {
     int64_t ldg;
     float *prep;                         // [n_models][PREP_SZ]
     void *prep_tc;                       // [n_models][TC_PREP_ELEMS] bf16, only when precision == 1
+    // precision 1: bf16 channel-chunk planes, the layout the tensor-core convolutions consume, written by the
+    // producing kernels and staged with bulk (TMA) copies.  Per sample: [C/8 planes][RUNP pixels][8 channels];
+    // pixel index r = y * (H + 2) + x (the padded grid's run of H rows; the two gap pixels after a row are zero).
+    uint16_t *a1p, *a2p, *dc2p, *dc3p, *zplane;
     int precision;                       // 0 = fp32 CUDA cores, 1 = bf16 tcgen05 convolutions
     float *glog;                         // [n_groups][2] loss sum, correct count (eval) / loss (train)
     int32_t *desc_i32;                   // scratch for generated descriptors (eval)

@@ -1,6 +1,7 @@
 // tcgen05 / TMEM / mbarrier building blocks (inline PTX, sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_bf16.h>
 #include <stdint.h>
 
 namespace dls {
@@ -21,6 +22,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "@p bra DONE;\n\t"
         "bra WAIT_LOOP;\n\t"
         "DONE:\n\t}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// eight fp32 values -> one 16-byte entry of a bf16 channel-chunk plane (round to nearest even)
+__device__ __forceinline__ uint4 pack8_bf16(const float (&o)[8]) {
+    __nv_bfloat162 q0 = __floats2bfloat162_rn(o[0], o[1]), q1 = __floats2bfloat162_rn(o[2], o[3]);
+    __nv_bfloat162 q2 = __floats2bfloat162_rn(o[4], o[5]), q3 = __floats2bfloat162_rn(o[6], o[7]);
+    uint4 v;
+    v.x = *reinterpret_cast<uint32_t *>(&q0); v.y = *reinterpret_cast<uint32_t *>(&q1);
+    v.z = *reinterpret_cast<uint32_t *>(&q2); v.w = *reinterpret_cast<uint32_t *>(&q3);
+    return v;
+}
+
+// ---- bulk asynchronous copies (TMA engine, no tensor map): global -> this CTA's shared memory ----
+// The copy completes on `bar` with complete_tx; the issuing thread announces the byte count with expect_tx.
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
 // ---- TMEM allocation (one full warp executes these) ----

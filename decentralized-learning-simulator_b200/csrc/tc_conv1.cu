@@ -349,7 +349,10 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
             const float rstd0 = 1.f / sqrtf(v0 * inv_n + GN_EPS), rstd1 = 1.f / sqrtf(v1 * inv_n + GN_EPS);
 
             if (valid) {
-                float *a1 = ws.a1 + (int64_t)slot * A1_SZ + pp * 32;
+                // the block output leaves as bf16 channel-chunk planes (what conv2 forward and the conv2 weight
+                // gradient stage with bulk copies): entry r = py * 17 + px of plane c8, 16 bytes; the thread of a
+                // row's last pixel also writes the two zero gap pixels that follow it
+                uint4 *a1p = reinterpret_cast<uint4 *>(ws.a1p + (int64_t)slot * A1P_SZ) + (py * 17 + px);
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     float o[8];
@@ -359,7 +362,12 @@ conv1_pool_tc_kernel(Pass p, Workspace ws, int save_bwd)
                         const float v = best[co] * (co < 16 ? rstd0 : rstd1) * prm[32 + co] + prm[64 + co];
                         o[e] = v > 0.f ? v : 0.f;
                     }
-                    tc::st_global_v8(a1 + c8 * 8, o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]);
+                    a1p[c8 * RUNP15] = tc::pack8_bf16(o);
+                    if (ws.a1) tc::st_global_v8(ws.a1 + (int64_t)slot * A1_SZ + pp * 32 + c8 * 8, o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]);
+                    if (px == 14 && py < 14) {
+                        a1p[c8 * RUNP15 + 1] = make_uint4(0u, 0u, 0u, 0u);
+                        a1p[c8 * RUNP15 + 2] = make_uint4(0u, 0u, 0u, 0u);
+                    }
                 }
             }
             if (save_bwd && t == 0) {
@@ -603,7 +611,9 @@ int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st)
     if (sms <= 0) sms = 148;
     int grid = n_slots < 2 * sms ? n_slots : 2 * sms;              // two persistent CTAs per SM
     if ((n_slots + grid - 1) / grid > C1P_CAP) grid = (n_slots + C1P_CAP - 1) / C1P_CAP;
-    conv1_pool_tc_kernel<<<grid, C1P_THREADS, C1P_SMEM, st>>>(p, ws, save ? 1 : 0);
+    Workspace w2 = ws;
+    if (!tune_value(TUNE_CONV_UNGROUPED)) w2.a1 = nullptr;          // only the bf16 planes a1p are consumed downstream
+    conv1_pool_tc_kernel<<<grid, C1P_THREADS, C1P_SMEM, st>>>(p, w2, save ? 1 : 0);
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -20,7 +20,7 @@ tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *_
     for (int i = t; i < a_bytes; i += 128) sa[i] = a_img[i];
     for (int i = t; i < b_bytes; i += 128) sb[i] = b_img[i];
     if (t == 0) { tc::mbar_init(&bar, 1); tc::mbar_fence_init(); }
-    if (warp == 0) tc::tmem_alloc(&tmem_base, 128);
+    if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -37,7 +37,7 @@ tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *_
         // throughput probe: re-issue the first (up to 8) MMAs `repeat` times into spare columns
         for (int r = 0; r < repeat; ++r) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) tc::mma_f16(tm + 64, ad[i], bd[i], idesc, 1u);
+            for (int i = 0; i < 8; ++i) tc::mma_f16(tm + 256, ad[i], bd[i], idesc, 1u);
         }
         tc::mma_commit(&bar);
     }
@@ -52,20 +52,81 @@ tc_probe_kernel(const uint8_t *__restrict__ a_img, int a_bytes, const uint8_t *_
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(tm, 128);
+    if (warp == 0) tc::tmem_dealloc(tm, 512);
+}
+
+// Contention probe: warp 4 issues `n_mma` MMAs (N = 96 columns at TMEM column 256) while warps 0-3 run `ld_loops`
+// rounds of three 32-column TMEM loads (and `shfl_per_round` warp shuffles) each.  cycles[0] = MMA stream,
+// cycles[1] = warp 0's load loop.
+__global__ void __launch_bounds__(160)
+tc_contention_kernel(int n_mma, int ld_loops, int shfl_per_round, long long *__restrict__ cycles, float *__restrict__ sink)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    const int t = threadIdx.x, warp = t >> 5;
+    for (int i = t; i < 32768; i += 160) reinterpret_cast<uint32_t *>(smem)[i] = 0u;
+    if (t == 0) { tc::mbar_init(&bar, 1); tc::mbar_fence_init(); }
+    if (warp == 0) tc::tmem_alloc(&tmem_base, 512);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tm = tmem_base;
+    if (warp == 4) {
+        if (t == 128) {
+            const uint32_t base = tc::smem_u32(smem);
+            const uint64_t ad = tc::smem_desc(base + 16, 4096, 128), bd = tc::smem_desc(base + 65536, 1536, 128);
+            const uint32_t idesc = tc::instr_desc_bf16(128, 96, 0, 0);
+            const long long t0 = clock64();
+            for (int i = 0; i < n_mma; ++i) tc::mma_f16(tm + 256, ad + (uint64_t)((i & 7) * 2), bd, idesc, 1u);
+            tc::mma_commit(&bar);
+            tc::mbar_wait(&bar, 0);
+            cycles[0] = clock64() - t0;
+        }
+    } else {
+        const long long t0 = clock64();
+        float acc = 0.f;
+        for (int r = 0; r < ld_loops; ++r) {
+            uint32_t a[32], b[32], c[32];
+            const uint32_t ta = tm + ((uint32_t)(warp * 32) << 16);
+            tc::tmem_ld32(ta, a); tc::tmem_ld32(ta + 32, b); tc::tmem_ld32(ta + 64, c);
+            tc::tmem_ld_wait();
+            float v = __uint_as_float(a[r & 31]) + __uint_as_float(b[r & 31]) + __uint_as_float(c[r & 31]);
+            for (int j = 0; j < shfl_per_round; ++j) v += __shfl_down_sync(0xffffffffu, v, 1);
+            acc += v;
+        }
+        if (t == 0) cycles[1] = clock64() - t0;
+        if (acc == 12345.f) sink[t] = acc;
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tm, 512);
 }
 
 }  // namespace dls
 
 using namespace dls;
 
+extern "C" int dls_tc_contention(int32_t n_mma, int32_t ld_loops, int32_t shfl_per_round, long long *cycles, float *sink,
+                                 void *stream)
+{
+    if (!cycles || !sink || n_mma < 0 || ld_loops < 0) return DLS_E_ARG;
+    const int smem = 132 * 1024;
+    cudaError_t e = cudaFuncSetAttribute(tc_contention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    tc_contention_kernel<<<1, 160, smem, (cudaStream_t)stream>>>(n_mma, ld_loops, shfl_per_round, cycles, sink);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+
 // a_desc / b_desc: descriptors with start-address field RELATIVE to the operand image (the kernel
-// adds the image's shared-memory address); out: [128 TMEM lanes][ncols] floats, ncols <= 64.
+// adds the image's shared-memory address); out: [128 TMEM lanes][ncols] floats, ncols <= 256.
 extern "C" int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, int32_t b_bytes,
                             const uint64_t *a_desc, const uint64_t *b_desc, int32_t n_mma, uint32_t idesc,
                             int32_t ncols, float *out, int32_t repeat, long long *cycles_out, void *stream)
 {
-    if (!a_img || !b_img || !a_desc || !b_desc || !out || n_mma <= 0 || ncols <= 0 || ncols > 64) return DLS_E_ARG;
+    if (!a_img || !b_img || !a_desc || !b_desc || !out || n_mma <= 0 || ncols <= 0 || ncols > 256) return DLS_E_ARG;
     const size_t smem = ((size_t)(a_bytes + 1023) & ~(size_t)1023) + (size_t)b_bytes + 1024;
     if (smem > 200 * 1024) return DLS_E_TOO_BIG;
     cudaError_t e = cudaFuncSetAttribute(tc_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

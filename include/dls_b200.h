@@ -183,6 +183,13 @@ int dls_tc_probe(const uint8_t *a_img, int32_t a_bytes, const uint8_t *b_img, in
                  int32_t ncols, float *out, int32_t repeat /* re-issue the first 8 MMAs this many times */,
                  long long *cycles_out /* optional: SM cycles for the repeated MMAs */, void *stream);
 
+/* Diagnostic: one CTA issues `n_mma` tcgen05.mma (M128 N96 K16, bf16) while four warps run `ld_loops` rounds of
+ * TMEM loads (3 x 32 columns) and `shfl_per_round` warp shuffles; cycles[0] = SM cycles of the MMA stream,
+ * cycles[1] = of the load loop.  Measures how the tensor pipe, TMEM reads and the shuffle path contend
+ * (scripts/probe_contention.py).  No reference counterpart. */
+int dls_tc_contention(int32_t n_mma, int32_t ld_loops, int32_t shfl_per_round, long long *cycles, float *sink,
+                      void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * test wave without a workspace argument.  This entry point has NO counterpart in the reference;
  * it exists for callers that cannot allocate device memory (a foreign-function binding that only

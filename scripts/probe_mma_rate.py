@@ -39,7 +39,14 @@ def main():
             ("K-major  M64  N32 ", 64, 32, 0, 0, 4096, 128, 512, 128),
             ("MN-major M64  N32 ", 64, 32, 1, 1, 128, 4096, 128, 4096),
             ("MN-major M64  N64 ", 64, 64, 1, 1, 128, 4096, 128, 4096),
-            ("MN-major M128 N32 ", 128, 32, 1, 1, 128, 2048, 128, 4096)]:
+            ("MN-major M128 N32 ", 128, 32, 1, 1, 128, 2048, 128, 4096),
+            ("K-major  M128 N96 A start +16 B", 128, 96, 0, 0, 4096, 128, 1536, 128, 16),
+            ("K-major  M128 N160 A start +16 B", 128, 160, 0, 0, 4096, 128, 2560, 128, 16),
+            ("K-major  M128 N256 A start +16 B", 128, 256, 0, 0, 4096, 128, 4096, 128, 16),
+            ("MN-major M128 N64 B start +16 B", 128, 64, 1, 1, 128, 2048, 128, 4096, 0, 16),
+            ("MN-major M128 N96 B start +16 B", 128, 96, 1, 1, 128, 2048, 128, 4096, 0, 16),
+            ("MN-major M128 N128 B start +16 B", 128, 128, 1, 1, 128, 2048, 128, 4096, 0, 16),
+            ("MN-major M128 N160 B start +16 B", 128, 160, 1, 1, 128, 2048, 128, 4096, 0, 16)]:
         a_off = rest[0] if len(rest) > 0 else 0
         b_off = rest[1] if len(rest) > 1 else 0
         ad = torch.tensor(np.array([desc(i * 256 + a_off, la, sa) for i in range(8)], dtype=np.uint64).view(np.int64), device=dev)

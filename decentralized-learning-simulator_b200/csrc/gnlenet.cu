@@ -474,7 +474,7 @@ classifier_kernel(Pass p, Workspace ws, int mode, float *loss_out, float *out_lo
 // overlapping windows in output-scan order (the order PyTorch's CPU kernel accumulates in).
 // ------------------------------------------------------------------------------------------
 template <int C, int H, int PH, bool POOL>
-__global__ void __launch_bounds__(256, (POOL && H == 15) ? 6 : 4)
+__global__ void __launch_bounds__(256, (POOL && H == 15) ? 4 : 4)
 gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout,
                     const uint8_t *__restrict__ idx, const float *__restrict__ cpre,
                     const float *__restrict__ stats, float *__restrict__ dc, float *__restrict__ gnp,
@@ -499,43 +499,58 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     const float gam = row[gw_off + ch];
     const float cb = cbias_off >= 0 ? row[cbias_off + ch] : 0.f;    // `cpre` without the conv bias (tensor-core path)
 
+    // Every global load of the sample is issued up front — the pooled gradients with their ReLU masks and arg-max
+    // bytes, and the pre-norm activations — so the kernel pays ONE memory latency instead of one per phase.
+    constexpr int NE = (SZ + 255) / 256;
+    constexpr int NP = POOL ? (OSZ + 255) / 256 : 1;
+    float xh[NE];
+    float pv[NP];
+    int ppos[NP], pcol[NP];
+    if (POOL) {
+        const uint8_t *is = idx + (int64_t)slot * OSZ;
+#pragma unroll
+        for (int k = 0; k < NP; ++k) {
+            const int o = t + k * 256;
+            pv[k] = 0.f; ppos[k] = 0; pcol[k] = -1;
+            if (o < OSZ) {
+                const int c = o % C, pp = o / C, py = pp / PH, px = pp - py * PH;
+                const int li = is[o];
+                pv[k] = as[o] > 0.f ? das[o] : 0.f;
+                ppos[k] = ((2 * py + li / 3) * H + 2 * px + li % 3) * C + c;
+                pcol[k] = (py & 1) * 2 + (px & 1);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        const int e = t + k * 256;
+        xh[k] = e < SZ ? cp[e] : 0.f;
+    }
     if (POOL) {
         // route each pooled gradient to the arg-max position of its 3x3/2 window.  Windows of one colour
         // (py%2, px%2) are disjoint, so four passes add without races and in a fixed order.
-        const uint8_t *is = idx + (int64_t)slot * OSZ;
         for (int e = t; e < SZ; e += 256) dg[e] = 0.f;
         __syncthreads();
 #pragma unroll
         for (int colour = 0; colour < 4; ++colour) {
-            const int cy = colour >> 1, cx = colour & 1;
-            const int ny = (PH - cy + 1) / 2, nx = (PH - cx + 1) / 2;
-            for (int i = t; i < ny * nx * C; i += 256) {
-                const int c = i % C, w = i / C, py = 2 * (w / nx) + cy, px = 2 * (w % nx) + cx;
-                const int o = (py * PH + px) * C + c;
-                if (as[o] > 0.f) {
-                    const int li = is[o];
-                    dg[((2 * py + li / 3) * H + 2 * px + li % 3) * C + c] += das[o];
-                }
-            }
+#pragma unroll
+            for (int k = 0; k < NP; ++k)
+                if (pcol[k] == colour && pv[k] != 0.f) dg[ppos[k]] += pv[k];
             __syncthreads();
         }
     }
     // One pass over the sample: x-hat and the incoming gradient stay in registers between the statistics
-    // and the output pass (the pre-norm activations are read from memory once).  Block 1 (no pooling in
-    // front of the ReLU) re-derives the ReLU mask from x-hat instead of reading the activations back.
-    constexpr int NE = (SZ + 255) / 256;
-    constexpr bool KEEP = !(POOL && H == 15);              // block 2 needs its registers for occupancy: it re-reads
-    float xh[KEEP ? NE : 1];
+    // and the output pass.  Block 1 (no pooling in front of the ReLU) re-derives the ReLU mask from x-hat instead
+    // of reading the activations back.
     const float bet = POOL ? 0.f : row[gw_off + C + ch];
     float s1 = 0.f, s2 = 0.f, dgam = 0.f, dbet = 0.f;     // 256 % C == 0: a thread only sees channel `ch`
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
         const int e = t + k * 256;
-        if (KEEP) xh[k] = 0.f;
         if (e < SZ) {
-            const float xhat = ((cp[e] + cb) - mean) * rstd;
+            const float xhat = ((xh[k] + cb) - mean) * rstd;
             const float d = POOL ? dg[e] : ((xhat * gam + bet) > 0.f ? das[e] : 0.f);
-            if (KEEP) xh[k] = xhat;
+            xh[k] = xhat;
             if (!POOL) dg[e] = d;                          // own element: no barrier needed before the second pass
             const float dxh = d * gam;
             s1 += dxh;
@@ -560,7 +575,7 @@ gn_block_bwd_kernel(const float *__restrict__ da, const float *__restrict__ aout
     for (int k = 0; k < NE; ++k) {
         const int e = t + k * 256;
         if (e < SZ) {
-            const float xhat = KEEP ? xh[k] : ((cp[e] + cb) - mean) * rstd;
+            const float xhat = xh[k];
             const float v = rstd * (dg[e] * gam - m1 - xhat * m2);
             if (planes) dg[e] = v;                         // own element: staged for the plane stores below
             else dst[e] = v;

@@ -716,7 +716,10 @@ int conv2_dgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 // (13 x 32 fp32 TMEM columns); it walks over all samples of the node, double buffering the
 // staged planes: warps 1-7 stage chunk c+1 while one thread of warp 0 issues the MMAs of chunk c.
 // ==========================================================================================
-template <int COUT, int H, int SB, bool PAIR = false, bool QUAD = false>
+// NIC = shifted copies of the INPUT planes (by 0, 2, 4 pixels) stacked along N: one MMA with N = 32 * NIC columns
+// then covers NIC horizontal tap positions and the dY operand (4 KB) is read from shared memory once for all of
+// them — 44 SM cycles for N = 32, 48 for N = 64, 56 for N = 96 (scripts/probe_mma_rate.py).
+template <int COUT, int H, int SB, bool PAIR = false, bool QUAD = false, int NIC = 1>
 struct WgradTcCfg {
     static constexpr int CIN = 32;
     using G = PlaneGeom<H>;
@@ -732,8 +735,10 @@ struct WgradTcCfg {
     static constexpr int PLANE_D = NPD * 16, PLANE_I = NPI * 16;
     static constexpr int MROWS = QUAD ? 4 * COUT : (PAIR ? 2 * COUT : 64);   // accumulator rows of one MMA
     static constexpr int DPLANES = MROWS / 8;                      // 8-channel dY planes (PAIR / QUAD: shifted copies)
-    static constexpr int BUF = DPLANES * PLANE_D + 4 * PLANE_I;
+    static constexpr int IPLANES = 4 * NIC;
+    static constexpr int BUF = DPLANES * PLANE_D + IPLANES * PLANE_I;
     static constexpr int SMEM = 2 * BUF + 128;
+    static_assert(SMEM <= 227 * 1024, "shared memory budget");
     static constexpr int TAPS0 = 13;                                // taps of CTA half 0; half 1 gets 12
 };
 
@@ -757,7 +762,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1)
 conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY, const uint16_t *__restrict__ in_pl,
                      const uint16_t *__restrict__ dy_pl, const uint16_t *__restrict__ zeros, Pass p, Workspace ws, int w_off)
 {
-    using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD>;
+    constexpr int NIC = PLANES ? (QUAD ? 2 : 3) : 1;         // input copies (bulk-copy staging only)
+    using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD, NIC>;
     static_assert(!QUAD || (PAIR && COUT == 32), "the quad variant is the four-copy form of the pair trick");
     static_assert(!PAIR || (C::NPD >= C::NVALID + C::DMAX), "shifted copies need spare plane entries");
     static_assert(C::NPI >= C::FULL && C::NPI >= C::KPIX + C::TAIL, "input planes must hold every padded pixel of the chunk");
@@ -798,7 +804,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         // ------------------------------ producer: bulk copies ------------------------------
         if (warp == 1 && tc::elect_one()) {
             constexpr int RUN = C::G::NORIG, RUNP = H == 15 ? RUNP15 : RUNP7, NCOPY = QUAD ? 4 : (PAIR ? 2 : 1);
-            constexpr uint32_t TX = (uint32_t)(SB * ((COUT / 8) * NCOPY + 4) * RUN * 16);
+            constexpr uint32_t TX = (uint32_t)(SB * ((COUT / 8) * NCOPY + 4 * NIC) * RUN * 16);
             for (int c = 0; c < n_chunks; ++c) {
                 const int b = c & 1;
                 if (c >= 2) tc::mbar_wait(&bars[2 + b], (uint32_t)(((c >> 1) - 1) & 1));
@@ -821,9 +827,11 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                         }
                     }
 #pragma unroll
-                    for (int ch = 0; ch < 4; ++ch)
-                        tc::bulk_g2s(sI + (uint32_t)(ch * C::PLANE_I + (s * C::NPS + 2 * C::PP + 2) * 16),
-                                     live ? isrc + ch * RUNP * 8 : zeros, RUN * 16, &bars[b]);
+                    for (int j = 0; j < NIC; ++j)            // copy j reads as the input shifted by 2j pixels
+#pragma unroll
+                        for (int ch = 0; ch < 4; ++ch)
+                            tc::bulk_g2s(sI + (uint32_t)((j * 4 + ch) * C::PLANE_I + (s * C::NPS + 2 * C::PP + 2 - 2 * j) * 16),
+                                         live ? isrc + ch * RUNP * 8 : zeros, RUN * 16, &bars[b]);
                 }
             }
         }
@@ -860,6 +868,8 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
         // warp-uniform control flow, one elected lane issues (no ELECT/BRA.U.ANY waterfall per MMA)
         const bool leader = tc::elect_one();
         const uint32_t idesc = tc::instr_desc_bf16(C::MROWS, 32, 1, 1);
+        const uint32_t idesc_n2 = tc::instr_desc_bf16(C::MROWS, 64, 1, 1), idesc_n3 = tc::instr_desc_bf16(C::MROWS, 96, 1, 1);
+        (void)idesc_n2; (void)idesc_n3;
         uint32_t acc = 0;
         uint32_t tshift[NMMA];                       // tap shift in 16-byte units (registers: loops are unrolled)
 #pragma unroll
@@ -885,9 +895,23 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
                 for (int j = 0; j < C::KPIX / 16; ++j) {
                     const uint64_t ad = ad0 + (uint64_t)(j * 16);
                     const uint64_t bdj = bd0 + (uint64_t)(j * 16);
+                    if (NIC == 1) {
 #pragma unroll
-                    for (int ti = 0; ti < NMMA; ++ti)
-                        if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
+                        for (int ti = 0; ti < NMMA; ++ti)
+                            if (ti < ntap) tc::mma_f16(tmem + (uint32_t)(ti * 32), ad, bdj + tshift[ti], idesc, acc);
+                    } else if (QUAD) {
+                        // accumulator tile ti = 3a + b <-> taps (2a + i, 2b + j'); b = 0, 1 in one N = 64 MMA, b = 2 alone
+#pragma unroll
+                        for (int a = 0; a < 3; ++a) {
+                            tc::mma_f16(tmem + (uint32_t)(3 * a * 32), ad, bdj + (uint64_t)(2 * a * C::PP), idesc_n2, acc);
+                            tc::mma_f16(tmem + (uint32_t)((3 * a + 2) * 32), ad, bdj + (uint64_t)(2 * a * C::PP + 4), idesc, acc);
+                        }
+                    } else {
+                        // accumulator tile ti = 3 ky + kxp <-> taps (ky, 2 kxp + copy): the three kxp in one N = 96 MMA
+#pragma unroll
+                        for (int ky = 0; ky < 5; ++ky)
+                            tc::mma_f16(tmem + (uint32_t)(3 * ky * 32), ad, bdj + (uint64_t)(ky * C::PP), idesc_n3, acc);
+                    }
                     acc = 1;
                 }
                 tc::mma_commit(&bars[2 + b]);          // buffer b may be refilled once these MMAs are done
@@ -954,10 +978,11 @@ static int launch_wgrad_tc(const float *in, const float *dY, const uint16_t *in_
 {
     using C = WgradTcCfg<COUT, H, SB, PAIR, QUAD>;
     if (in_pl && dy_pl) {
+        using CP = WgradTcCfg<COUT, H, SB, PAIR, QUAD, QUAD ? 2 : 3>;
         static PerDeviceOnce attrp;
-        int rc = ensure_dyn_smem(conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD, true>, C::SMEM, attrp);
+        int rc = ensure_dyn_smem(conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD, true>, CP::SMEM, attrp);
         if (rc) return rc;
-        conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD, true><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, C::SMEM, st>>>(
+        conv_wgrad_tc_kernel<COUT, H, SB, PAIR, QUAD, true><<<p.n_groups * (PAIR ? 1 : 2), WG_THREADS, CP::SMEM, st>>>(
             in, dY, in_pl, dy_pl, ws.zplane, p, ws, w_off);
         DLS_LAUNCH_CHECK();
         return 0;

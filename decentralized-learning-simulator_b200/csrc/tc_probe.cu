@@ -90,6 +90,18 @@ tc_contention_kernel(int n_mma, int ld_loops, int shfl_per_round, long long *__r
         for (int r = 0; r < ld_loops; ++r) {
             uint32_t a[32], b[32], c[32];
             const uint32_t ta = tm + ((uint32_t)(warp * 32) << 16);
+            if (shfl_per_round == -1) {            // shape probe: 16-column loads, six per round (same bytes as 3 x 32)
+                uint32_t q0[16], q1[16], q2[16], q3[16], q4[16], q5[16];
+                tc::tmem_ld16(ta, q0); tc::tmem_ld16(ta + 16, q1); tc::tmem_ld16(ta + 32, q2);
+                tc::tmem_ld16(ta + 48, q3); tc::tmem_ld16(ta + 64, q4); tc::tmem_ld16(ta + 80, q5);
+                tc::tmem_ld_wait();
+                acc += __uint_as_float(q0[r & 15]) + __uint_as_float(q1[r & 15]) + __uint_as_float(q2[r & 15]) +
+                       __uint_as_float(q3[r & 15]) + __uint_as_float(q4[r & 15]) + __uint_as_float(q5[r & 15]);
+                continue;
+            }
+            if (shfl_per_round == -2) {            // one warp only does the loads (others idle): per-warp bandwidth
+                if (warp != 0) break;
+            }
             tc::tmem_ld32(ta, a); tc::tmem_ld32(ta + 32, b); tc::tmem_ld32(ta + 64, c);
             tc::tmem_ld_wait();
             float v = __uint_as_float(a[r & 31]) + __uint_as_float(b[r & 31]) + __uint_as_float(c[r & 31]);

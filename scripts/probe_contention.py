@@ -8,7 +8,7 @@ from dls_b200 import _lib
 dev = torch.device("cuda:0")
 cyc = torch.zeros(2, dtype=torch.int64, device=dev); sink = torch.zeros(256, device=dev)
 lib = _lib.lib()
-for n_mma, loops, shfl in [(2000, 0, 0), (0, 200, 0), (2000, 200, 0), (2000, 100, 0), (0, 200, 64), (2000, 200, 64), (2000, 100, 64), (0, 200, 256), (2000, 100, 256)]:
+for n_mma, loops, shfl in [(2000, 0, 0), (0, 200, 0), (2000, 200, 0), (2000, 100, 0), (0, 200, 64), (2000, 200, 64), (2000, 100, 64), (0, 200, 256), (2000, 100, 256), (0, 200, -1), (0, 200, -2)]:
     cyc.zero_()
     rc = lib.dls_tc_contention(n_mma, loops, shfl, cyc.data_ptr(), sink.data_ptr(), torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()

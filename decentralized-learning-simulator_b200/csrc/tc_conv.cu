@@ -345,7 +345,7 @@ struct ConvTc3Cfg : ConvTcCfg<CIN, COUT, H, SB> {
     static constexpr int RING = 8;                                     // boundary ring: tiles in flight between epilogue and finisher
     static constexpr int RQ = 64;                                      // floats per (quadrant, channel group): r1(lane 0), partial(lane 31)
     static constexpr int RING_FLOATS = RING * 4 * NCG * RQ;
-    static constexpr int SMEM = Base::B_BYTES + NST * Base::A_BYTES + RING_FLOATS * 4 + 256;
+    static constexpr int SMEM = Base::B_BYTES + NST * Base::A_BYTES + RING_FLOATS * 4 + 320;
     static constexpr int RUN = Base::NORIG;                            // pixels of a sample's plane run
     static constexpr int RUNP = H == 15 ? RUNP15 : RUNP7;              // plane stride (pixels) in global memory
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
@@ -384,8 +384,8 @@ conv_tc3_kernel(const float *__restrict__ in, const uint16_t *__restrict__ in_pl
     float *ring = reinterpret_cast<float *>(sA0 + NST * C::A_BYTES);   // [RING][4 quadrants][NCG][RQ]
     uint64_t *bars = reinterpret_cast<uint64_t *>(ring + C::RING_FLOATS);
     uint64_t *full = bars, *empty = bars + NST, *tfull = bars + 2 * NST, *tempty = tfull + 2;
-    uint64_t *rfull = tempty + 2, *rempty = rfull + RING;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(rempty + RING);
+    uint64_t *rfull = tempty + 2, *rempty = rfull + RING, *wbar = rempty + RING;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(wbar + 1);
 
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int parts = (p.gs + spc - 1) / spc;
@@ -401,14 +401,12 @@ conv_tc3_kernel(const float *__restrict__ in, const uint16_t *__restrict__ in_pl
     model_row(p, g, m);
 
     {
-        const uint4 *src = reinterpret_cast<const uint4 *>(wprep + (int64_t)m * TC_PREP_ELEMS + wprep_off);
-        uint4 *dst = reinterpret_cast<uint4 *>(sB);
-        for (int i = t; i < C::B_BYTES / 16; i += CT3_THREADS) dst[i] = __ldg(src + i);
         uint4 *za = reinterpret_cast<uint4 *>(sA0);
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         for (int i = t; i < NST * C::A_BYTES / 16; i += CT3_THREADS) za[i] = z;
     }
     if (t == 0) {
+        tc::mbar_init(wbar, 1);
         for (int i = 0; i < NST; ++i) { tc::mbar_init(&full[i], PLANES ? 1 : CT3_PRODUCERS); tc::mbar_init(&empty[i], 1); }
         tc::mbar_init(&tfull[0], 1); tc::mbar_init(&tfull[1], 1);
         tc::mbar_init(&tempty[0], 128); tc::mbar_init(&tempty[1], 128);
@@ -470,6 +468,12 @@ conv_tc3_kernel(const float *__restrict__ in, const uint16_t *__restrict__ in_pl
     } else if (warp == 4) {
         // ------------------------------ MMA issuer ------------------------------
         const bool leader = tc::elect_one();
+        if (leader) {                                                  // the node's weights: one bulk copy (TMA engine)
+            tc::mbar_expect_tx(wbar, (uint32_t)C::B_BYTES);
+            tc::bulk_g2s(tc::smem_u32(sB), wprep + (int64_t)m * TC_PREP_ELEMS + wprep_off, (uint32_t)C::B_BYTES, wbar);
+        }
+        __syncwarp();
+        tc::mbar_wait(wbar, 0);
         const uint32_t idesc2 = tc::instr_desc_bf16(128, 2 * COUT, 0, 0);
         const uint32_t idesc1 = tc::instr_desc_bf16(128, COUT, 0, 0);
         const uint64_t bdA = tc::smem_desc(tc::smem_u32(sB), 2 * COUT * 16, 128);                           // kx = 0, 1

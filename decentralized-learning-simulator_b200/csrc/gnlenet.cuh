@@ -36,6 +36,19 @@ constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
 constexpr int TC_PREP_ELEMS = 2 * 25600 + 2 * 51200 + 2560;   // bf16 UMMA-layout weight copies per model (tc_conv.cu)
 constexpr int PREP_SZ = 2 * W2T_SZ + 2 * W3T_SZ;   // W2t, W2d, W3t, W3d per model
 
+// Optimizer update fused into the conv2 / conv3 weight-gradient epilogues (train waves, tensor-core path): the
+// gradient of those 76 800 weights never goes to memory; torch.optim.SGD semantics as in sgd_update_kernel.
+struct SgdFuse {
+    float *X = nullptr;                  // stacked parameters (nullptr: not fused, gradients go to G)
+    int64_t ldx = 0;
+    float *M = nullptr;                  // momentum rows (nullptr when mu == 0)
+    int64_t ldm = 0;
+    const int32_t *task_row = nullptr;   // [n_groups] row of X
+    const int32_t *task_peer = nullptr;  // [n_groups] row of M
+    const uint8_t *first = nullptr;      // [n_groups] 1: the node has no momentum buffer yet (nullptr: none is first)
+    float lr = 0.f, mu = 0.f, wd = 0.f;
+};
+
 // All activations are NHWC fp32, one contiguous record per sample slot.
 struct Workspace {
     // forward (kept for backward)
@@ -52,6 +65,7 @@ struct Workspace {
     // producing kernels and staged with bulk (TMA) copies.  Per sample: [C/8 planes][RUNP pixels][8 channels];
     // pixel index r = y * (H + 2) + x (the padded grid's run of H rows; the two gap pixels after a row are zero).
     uint16_t *a1p, *a2p, *dc2p, *dc3p, *zplane;
+    SgdFuse sgd;                         // set by dls_train_wave for the duration of a step
     int precision;                       // 0 = fp32 CUDA cores, 1 = bf16 tcgen05 convolutions
     float *glog;                         // [n_groups][2] loss sum, correct count (eval) / loss (train)
     int32_t *desc_i32;                   // scratch for generated descriptors (eval)

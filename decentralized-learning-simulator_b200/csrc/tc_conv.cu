@@ -963,10 +963,43 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
             }
         }
         __syncthreads();
-        float *Gh = G + half * TR * 800;
-        for (int i = t; i < TR * 800; i += WG_THREADS) {
-            const int co = i / 800, rem = i - co * 800;
-            Gh[i] = sT[co * 801 + rem];
+        if (ws.sgd.X) {
+            // fused optimizer step on these TR x 800 weights (g += wd p; buf = g on the node's first step, else
+            // buf = mu buf + g; p -= lr buf — the arithmetic of sgd_update_kernel)
+            const SgdFuse &o = ws.sgd;
+            float *xr = o.X + (int64_t)o.task_row[g] * o.ldx + w_off + half * TR * 800;
+            float *mr = (o.M && o.mu != 0.f) ? o.M + (int64_t)o.task_peer[g] * o.ldm + w_off + half * TR * 800 : nullptr;
+            const bool fst = o.first ? (o.first[g] != 0) : false;
+            constexpr int U = 10;                                  // independent loads in flight per thread
+            for (int i0 = t; i0 < TR * 800; i0 += U * WG_THREADS) {
+                float pv[U], mv[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * WG_THREADS;
+                    pv[u] = i < TR * 800 ? xr[i] : 0.f;
+                    mv[u] = (mr && !fst && i < TR * 800) ? mr[i] : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = i0 + u * WG_THREADS;
+                    if (i >= TR * 800) break;
+                    const int co = i / 800, rem = i - co * 800;
+                    float gv = sT[co * 801 + rem];
+                    if (o.wd != 0.f) gv = fmaf(o.wd, pv[u], gv);
+                    if (mr) {
+                        const float bv = fst ? gv : __fadd_rn(__fmul_rn(mv[u], o.mu), gv);
+                        mr[i] = bv;
+                        gv = bv;
+                    }
+                    xr[i] = fmaf(-o.lr, gv, pv[u]);
+                }
+            }
+        } else {
+            float *Gh = G + half * TR * 800;
+            for (int i = t; i < TR * 800; i += WG_THREADS) {
+                const int co = i / 800, rem = i - co * 800;
+                Gh[i] = sT[co * 801 + rem];
+            }
         }
         __syncthreads();
     }

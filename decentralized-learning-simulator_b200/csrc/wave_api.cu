@@ -20,8 +20,9 @@ __global__ void __launch_bounds__(256)
 sgd_update_kernel(float *__restrict__ X, int64_t ldx, float *__restrict__ M, int64_t ldm,
                   const float *__restrict__ G, int64_t ldg, const int32_t *__restrict__ task_row,
                   const int32_t *__restrict__ task_peer, const uint8_t *__restrict__ first,
-                  const int32_t *__restrict__ gcount, int64_t P, float lr, float mu, float wd)
+                  const int32_t *__restrict__ gcount, int64_t P, float lr, float mu, float wd, int skip0, int skip1)
 {
+    // [skip0, skip1): parameters already updated by the weight-gradient epilogues (SgdFuse)
     const int g = blockIdx.y;
     if (gcount[g] <= 0) return;
     float *x = X + (int64_t)task_row[g] * ldx;
@@ -30,6 +31,7 @@ sgd_update_kernel(float *__restrict__ X, int64_t ldx, float *__restrict__ M, int
     const bool fst = first ? (first[g] != 0) : false;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P;
          i += (int64_t)gridDim.x * blockDim.x) {
+        if (i >= skip0 && i < skip1) continue;
         float gv = gr[i];
         const float pv = x[i];
         if (wd != 0.f) gv = fmaf(wd, pv, gv);
@@ -194,7 +196,7 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
                 return rcf;
             dim3 grid(128, n_tasks);
             sgd_update_kernel<<<grid, 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
-                                                     s == 0 ? mom_first : nullptr, p.gcount, DLS_FEMNIST_P, lr, mu, wd);
+                                                     s == 0 ? mom_first : nullptr, p.gcount, DLS_FEMNIST_P, lr, mu, wd, 0, 0);
             DLS_LAUNCH_CHECK();
         }
         return 0;
@@ -246,11 +248,35 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
             p.img_idx = mb_index + ((int64_t)s * n_tasks + off) * batch;
             p.gcount = mb_count + (int64_t)s * n_tasks + off;
             p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
+            // tensor-core path: the conv2 / conv3 weights (OFF_W2 .. OFF_B2 and OFF_W3 .. OFF_B3) are updated inside
+            // their weight-gradient kernels; the update kernel below then only walks the rest of the row
+            const bool fuse = precision == 1 && !tune_value(TUNE_CONV_UNGROUPED) && !tune_value(TUNE_NO_SGD_FUSE);
+            ws[h].sgd = gnl::SgdFuse();
+            if (fuse) {
+                gnl::SgdFuse &o = ws[h].sgd;
+                o.X = X; o.ldx = ldx; o.M = M; o.ldm = ldm; o.task_row = task_row + off; o.task_peer = task_peer + off;
+                o.first = (s == 0 && mom_first) ? mom_first + off : nullptr;
+                o.lr = lr; o.mu = mu; o.wd = wd;
+            }
             if ((rc = gnl_step(p, ws[h], loss_out ? loss_out + (int64_t)s * n_tasks + off : nullptr, sh, h))) return rc;
+            // two launches around the fused ranges: [0, OFF_W2) + [OFF_B2, OFF_W3) in one grid, [OFF_B3, P) in the other
+            if (fuse) {
+                dim3 g1(4, nt);
+                sgd_update_kernel<<<g1, 256, 0, sh>>>(X, ldx, M, ldm, ws[h].G, ws[h].ldg, task_row + off, task_peer + off,
+                                                      (s == 0 && mom_first) ? mom_first + off : nullptr, p.gcount,
+                                                      gnl::OFF_W3, lr, mu, wd, gnl::OFF_W2, gnl::OFF_B2);
+                DLS_LAUNCH_CHECK();
+                sgd_update_kernel<<<g1, 256, 0, sh>>>(X + gnl::OFF_B3, ldx, M ? M + gnl::OFF_B3 : nullptr, ldm,
+                                                      ws[h].G + gnl::OFF_B3, ws[h].ldg, task_row + off, task_peer + off,
+                                                      (s == 0 && mom_first) ? mom_first + off : nullptr, p.gcount,
+                                                      gnl::P - gnl::OFF_B3, lr, mu, wd, 0, 0);
+                DLS_LAUNCH_CHECK();
+                continue;
+            }
             dim3 grid(32, nt);
             sgd_update_kernel<<<grid, 256, 0, sh>>>(X, ldx, M, ldm, ws[h].G, ws[h].ldg, task_row + off, task_peer + off,
                                                     (s == 0 && mom_first) ? mom_first + off : nullptr, p.gcount, gnl::P,
-                                                    lr, mu, wd);
+                                                    lr, mu, wd, 0, 0);
             DLS_LAUNCH_CHECK();
         }
     }

@@ -35,6 +35,7 @@ class DeviceDataset:
         # local partition index of a global node id
         ids = list(node_ids) if node_ids is not None else list(range(first_node, first_node + self.n_nodes))
         self.local_of = {int(n): i for i, n in enumerate(ids)}
+        self.sizes = None           # per-partition sample counts when partitions are ragged (cifar_cache.open_cache)
 
     @classmethod
     def synthetic(cls, layout: ModelLayout, n_nodes: int, n_i: int, n_test: int, device, seed: int = 42,
@@ -69,6 +70,8 @@ class DeviceDataset:
         may be partial (dasklearn/model_trainer.py:99-102)."""
         T, S = len(peers), (max(steps) if len(steps) else 0)
         base = np.array([self.local_of[int(q)] * self.n_i for q in peers], dtype=np.int64).reshape(T, 1)
+        if self.sizes is not None:
+            return self._minibatches_ragged(peers, rounds, batch, steps, base)
         if self.permutation is synthetic.minibatch_permutation:
             perm = synthetic.minibatch_permutations(self.seed, peers, rounds, self.n_i)     # one argsort per wave
         else:
@@ -80,5 +83,19 @@ class DeviceDataset:
         padded[:, :m] = perm[:, :m] + base
         padded[np.arange(S * batch).reshape(1, -1) >= steps_a * batch] = -1          # per-task local_steps
         idx = np.ascontiguousarray(padded.reshape(T, S, batch).transpose(1, 0, 2)).astype(np.int32)
+        cnt = (idx >= 0).sum(axis=2).astype(np.int32)
+        return idx, cnt
+
+    def _minibatches_ragged(self, peers, rounds, batch, steps, base):
+        """Partitions of different sizes (real data, Dirichlet splits): node q draws a permutation of ITS n_q samples;
+        it runs min(steps, ceil(n_q / batch)) steps and its last batch may be partial (model_trainer.py:99-102)."""
+        T, S = len(peers), (max(steps) if len(steps) else 0)
+        idx = -np.ones((S, T, batch), dtype=np.int32)
+        for t, (q, r) in enumerate(zip(peers, rounds)):
+            n_q = int(self.sizes[self.local_of[int(q)]])
+            perm = self.permutation(self.seed, int(q), int(r), n_q)[:int(steps[t]) * batch]
+            full = np.full(S * batch, -1, dtype=np.int64)
+            full[:len(perm)] = perm + base[t, 0]
+            idx[:, t, :] = full.reshape(S, batch)
         cnt = (idx >= 0).sum(axis=2).astype(np.int32)
         return idx, cnt

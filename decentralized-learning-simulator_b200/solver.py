@@ -440,15 +440,25 @@ class BatchedSolver:
                 ex.refs[s] = n
 
     def run(self, timing: bool = False):
+        """Solve the graph.  `timing`: per-wave durations in `wave_times` as (func, n_tasks, ms) — CUDA events on the
+        launching stream (host clock for a CPU stand-in executor)."""
+        import time as _time
         ex = self.ex
+        on_gpu = getattr(ex.device, "type", "cpu") == "cuda"
         results: Dict[str, List[RowHandle]] = {}
         for w in self._stream():
             if timing:
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
+                if on_gpu:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                else:
+                    e0 = _time.perf_counter()
             self.run_wave(w)
             if timing:
-                e1.record()
+                if on_gpu:
+                    e1.record()
+                else:
+                    e1 = _time.perf_counter()
                 self.wave_times.append((w.func, len(w.names), e0, e1))
             for name in w.names:
                 if name in self.sink_slots:
@@ -458,8 +468,11 @@ class BatchedSolver:
                         self.on_sink(name, res)
         self.finish()
         if timing:
-            torch.cuda.synchronize()
-            self.wave_times = [(f, n, e0.elapsed_time(e1)) for f, n, e0, e1 in self.wave_times]
+            if on_gpu:
+                torch.cuda.synchronize()
+                self.wave_times = [(f, n, e0.elapsed_time(e1)) for f, n, e0, e1 in self.wave_times]
+            else:
+                self.wave_times = [(f, n, (e1 - e0) * 1e3) for f, n, e0, e1 in self.wave_times]
         return results
 
     def run_with_loss(self):

@@ -165,8 +165,12 @@ class DistributedSolver(BatchedSolver):
                 else:
                     names = next(zip(*ins))
                     l = 1 + max(map(lvl_get, names))
-                    owners = set(map(own_get, names))
-                    cut = len(owners) > 1 or o not in owners
+                    # the owners of the inputs only matter until the level is known to be an exchange level
+                    if l in xchg_levels and t["func"] == "aggregate":
+                        cut = False
+                    else:
+                        owners = set(map(own_get, names))
+                        cut = len(owners) > 1 or o not in owners
                 level_of[name] = l
                 if cut:
                     if t["func"] != "aggregate":
@@ -198,6 +202,8 @@ class DistributedSolver(BatchedSolver):
         if self.transport == "push":
             # static halo numbering: node p's row lands in slot (index of p among the nodes rank q does not own)
             self._remote_index = [None] * self.world
+            counts = np.bincount(self.owner_of, minlength=self.world)
+            self._n_remote = [int(len(self.owner_of) - c) for c in counts]
         # the base planner only looks at this rank's tasks
         out = [[] for _ in range(n_levels)]
         for n in mine:
@@ -217,15 +223,16 @@ class DistributedSolver(BatchedSolver):
         return r
 
     def _push_slots(self, q: int, rows):
-        """Halo slots (without the parity offset) on rank q for `rows` = sorted [(peer, task, idx)] coming from ONE
-        source rank: slot = remote index of the peer + version * n_remote, the version counting rows of the same
-        node within this level.  Receiver and sender evaluate this on the same list, so they agree."""
+        """Halo slots (without the parity offset) on rank q for `rows` = [(peer, task, idx)], sorted by (task, idx),
+        coming from ONE source rank: slot = remote index of the peer + version * n_remote, the version counting rows
+        of the same node within this level in list order.  Receiver and sender evaluate this on the same list, so
+        they agree."""
         ridx = self._remote_idx(q)
-        n_remote = int((self.owner_of != q).sum())
-        out, last, v = [], None, 0
+        n_remote = self._n_remote[q]
+        out, seen = [], {}
         for peer, _, _ in rows:
-            v = v + 1 if peer == last else 0
-            last = peer
+            v = seen.get(peer, 0)
+            seen[peer] = v + 1
             if v >= self.HALO_VERSIONS:
                 raise RuntimeError("push transport: more than %d live rows of node %d needed by rank %d at one level; "
                                    "use transport='a2a'" % (self.HALO_VERSIONS, peer, q))
@@ -248,10 +255,11 @@ class DistributedSolver(BatchedSolver):
         for q, m in self._remote.get(level, ()):              # one reference per consuming remote task
             pending_release.append(vs[m])
             send[q].add(m)
-        # both ends order a (source rank -> destination rank) row list the same way: by producer peer, task, index
-        key = self._halo_key
-        recv_l = [sorted(map(key, x)) for x in recv]
-        send_l = [sorted(map(key, x)) for x in send]
+        # both ends order a (source rank -> destination rank) row list the same way: by (task name, index) — plain
+        # tuple comparison — and attach the producer's peer
+        peer_of = lambda m: tasks[m[0]]["data"]["peer"]
+        recv_l = [[(peer_of(m), m[0], m[1]) for m in sorted(x)] for x in recv]
+        send_l = [[(peer_of(m), m[0], m[1]) for m in sorted(x)] for x in send]
         self._halo_of = {}
         n_recv = sum(len(x) for x in recv_l)
         n_send = sum(len(x) for x in send_l)

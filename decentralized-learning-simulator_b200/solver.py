@@ -182,7 +182,7 @@ class BatchedSolver:
 
         # single-GPU solve: every model reference is a pool slot (no halo rows) -> plain dictionary lookups
         local_only = type(self)._model_slot is BatchedSolver._model_slot
-        model_slot = value_slot.__getitem__ if local_only else self._model_slot
+        model_slot = value_slot.__getitem__ if local_only else value_slot.get
         for li, names in enumerate(self.levelise()):
             by_func: Dict[str, Wave] = {}
             # a level may hold two train tasks of one node only in malformed graphs; detect in executor
@@ -236,6 +236,9 @@ class BatchedSolver:
                     except TypeError:                                # lists (e.g. a JSON round trip)
                         refs = [tuple(m) for m in refs]
                         ms = list(map(model_slot, refs))
+                    if not local_only and None in ms:                # rows of other GPUs: halo references (negative)
+                        halo = self._halo_of
+                        ms = [-1 - halo[m] if x is None else x for x, m in zip(ms, refs)]
                     slot = take()
                     w.model_slots.append(ms)
                     wts = d.get("weights")

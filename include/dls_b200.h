@@ -44,8 +44,11 @@ const char *dls_build_info(void);
 /* Number of kernels this library has launched in the calling process (all entry points). */
 int64_t     dls_launch_count(void);
 /* Diagnostic knobs for experiments (scripts/): key 0 = aggregate tile width in float4 columns, 1 = aggregate
- * pipeline stages, 2 = number of equal lanes a train wave is split into; value 0 restores the automatic
- * choice.  Process-wide, not thread-safe, never needed for correct results.  No reference counterpart. */
+ * pipeline stages, 2 = number of equal lanes a train wave is split into, 3 = 1: round-1 tensor-core convolution
+ * kernels (one MMA per tap, fp32 activations converted by producer warps) instead of the plane / bulk-copy /
+ * tap-pair kernels, 5 = 1: separate optimizer kernel for the whole row instead of the update fused into the
+ * weight-gradient kernels; value 0 restores the default.  Process-wide, not thread-safe, never needed for correct
+ * results.  No reference counterpart. */
 int         dls_tune(int32_t key, int32_t value);
 
 /* ------------------------------------------------------------------------------------------

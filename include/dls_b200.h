@@ -126,7 +126,8 @@ int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_rows, const ui
  *                 may be NULL when mu == 0
  *   mom_first[t]  1 if node task_peer[t] has no momentum buffer yet (buf = grad on its first step)
  *   images/labels the nodes' uint8 HWC partitions, image i at images + i*img_bytes
- *   mb_index      [n_steps][n_tasks][batch] GLOBAL image ids (-1 = empty slot)
+ *   mb_index      [n_steps][n_tasks][batch] GLOBAL image ids (-1 = empty slot; the empty slots of a task's
+ *                 minibatch are its LAST ones: a partial batch fills a prefix)
  *   mb_count      [n_steps][n_tasks] delivered batch size (0 = task already finished its loader)
  *   loss_out      optional [n_steps][n_tasks] mean minibatch loss
  * Loss: NLL of log_softmax (GNLeNet) / cross entropy (FEMNIST), mean over the delivered batch.

@@ -174,3 +174,20 @@ def test_metric_size_wave_all_variants_agree(cuda):
     for r in range(0, n, 128):
         want = O.fedavg_numpy([Xh[s, :L.P] for s in lists[r]])
         assert np.array_equal(outs[4][r].cpu().numpy().view(np.uint32), want.view(np.uint32))
+
+
+def test_push_rows_to_device_addresses(cuda):
+    """dls_push_rows (the multi-GPU halo push) with destinations given as raw device addresses — here rows of a
+    second local tensor, on several GPUs rows of the peers' symmetric-memory halo.  Ragged tail (P % 4 != 0 is padded
+    by the row pitch), many transfers and a single one."""
+    X = torch.randn((40, L.ld), device=cuda)
+    H = torch.full((64, L.ld), float("nan"), device=cuda)
+    for src, dst in (([3], [7]), (list(range(0, 40, 3)), list(range(63, 63 - 14, -1)))):
+        s = torch.tensor(src, dtype=torch.int32, device=cuda)
+        d = torch.tensor([H.data_ptr() + r * L.ld * 4 for r in dst], dtype=torch.int64, device=cuda)
+        K.push_rows(X, s, d, L.P)
+        torch.cuda.synchronize()
+        for a, b in zip(src, dst):
+            assert torch.equal(H[b, :L.P], X[a, :L.P])
+    untouched = [r for r in range(64) if r not in (7, *range(63, 63 - 14, -1))]
+    assert bool(torch.isnan(H[untouched]).all())

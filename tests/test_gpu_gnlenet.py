@@ -183,3 +183,36 @@ def test_train_wave_many_nodes_vs_oracle(cuda, data):
         np.testing.assert_allclose(loss[:, t].cpu().numpy(), np.array(losses), rtol=1e-3)
     # untouched momentum row stays untouched
     assert np.array_equal(Mg[3], Mh[3])
+
+
+def test_kernel_variants_agree(cuda, data):
+    """The tensor-core path's build-time alternatives, switched with dls_tune: the optimizer update fused into the
+    weight-gradient epilogues must give the bits of the separate update kernel, and the plane / bulk-copy / tap-pair
+    convolution kernels must agree with the round-1 kernels (one MMA per tap) to accumulation-order noise."""
+    from dls_b200 import _lib
+    imgs, labs = data
+    n, n_i, steps, B = 5, 80, 3, 32
+    peers = [4, 0, 2, 5, 1]
+    idx, cnt = synthetic.minibatch_index(42, peers, [1] * n, n_i, B, steps)
+    gidx = np.where(idx >= 0, idx + np.array(peers)[:, None, None] * n_i, -1).astype(np.int32)
+    out = {}
+    try:
+        for name, key, val in (("default", 5, 0), ("unfused", 5, 1), ("round1_convs", 3, 1)):
+            _lib.lib().dls_tune(3, 0); _lib.lib().dls_tune(5, 0)
+            _lib.lib().dls_tune(key, val)
+            Xd = torch.from_numpy(perturbed_rows(n, seed=5)).to(cuda)
+            Md = torch.zeros((6, L.ld), device=cuda)
+            K.train_wave(L, Xd, Md, torch.arange(n, dtype=torch.int32, device=cuda),
+                         torch.tensor(peers, dtype=torch.int32, device=cuda), torch.ones(n, dtype=torch.uint8, device=cuda),
+                         torch.from_numpy(imgs.reshape(-1, 3072)).to(cuda), torch.from_numpy(labs.reshape(-1)).to(cuda),
+                         torch.from_numpy(np.ascontiguousarray(gidx.transpose(1, 0, 2))).to(cuda),
+                         torch.from_numpy(np.ascontiguousarray(cnt.T)).to(cuda), B, 0.002, 0.9, 0.0, K.Workspace(cuda),
+                         precision=1)
+            torch.cuda.synchronize()
+            out[name] = (Xd[:, :L.P].cpu().numpy(), Md[:, :L.P].cpu().numpy())
+    finally:
+        _lib.lib().dls_tune(3, 0); _lib.lib().dls_tune(5, 0)
+    assert np.array_equal(out["default"][0], out["unfused"][0]) and np.array_equal(out["default"][1], out["unfused"][1])
+    # different MMA grouping = different fp32 accumulation order; three momentum steps amplify it a little
+    rx, rm = rel(out["default"][0], out["round1_convs"][0]), rel(out["default"][1], out["round1_convs"][1])
+    assert rx < 3e-4 and rm < 3e-2, (rx, rm)

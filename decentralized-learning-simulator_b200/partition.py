@@ -107,8 +107,6 @@ class DistributedSolver(BatchedSolver):
         self.halo_bytes = 0
         self.transport = self._choose_transport(transport)
 
-    LEVEL_SLOTS = 4096       # exchange-level bitmap agreed on the host; deeper graphs take the global pass
-
     def _choose_transport(self, want: str) -> str:
         ex = self.ex
         have = getattr(ex, "transport", None)
@@ -116,15 +114,6 @@ class DistributedSolver(BatchedSolver):
             if want not in ("auto", have):
                 raise RuntimeError("executor already uses transport %r" % have)
             return have
-        # host-side group for the one tiny collective of planning (which levels exchange): it must not touch the
-        # GPU stream, or the host would wait for every kernel already queued
-        ex.side_group = None
-        try:
-            import torch.distributed as dist
-            if dist.is_initialized() and self.world > 1:
-                ex.side_group = self.group if dist.get_backend(self.group) == "gloo" else dist.new_group(backend="gloo")
-        except Exception:                             # noqa: BLE001 — no gloo: every rank scans the global list instead
-            ex.side_group = None
         if want == "a2a" or not hasattr(ex, "enable_symmetric"):
             got = "a2a"
         else:
@@ -150,91 +139,6 @@ class DistributedSolver(BatchedSolver):
         return self._task_owner[name]
 
     def levelise(self):
-        """Levels of this rank's tasks.  With a host-side process group the work is O(own tasks + their ancestors
-        + cut edges): levels come from a memoised walk over the inputs of the rank's own tasks (and of the remote
-        consumers of its outputs), and the set of levels at which ANY rank exchanges — every rank must enter the
-        exchange there — is agreed with one small host all_reduce.  Without such a group every rank scans the
-        whole task list (`_levelise_global`)."""
-        side = getattr(self.ex, "side_group", None)
-        if side is None:
-            return self._levelise_global()
-        import torch
-        import torch.distributed as dist
-        tasks, me = self.tasks, self.rank
-        owner_list = self.owner_of.tolist()
-        own: Dict[str, int] = {}
-        level_of: Dict[str, int] = {}
-
-        def owner(name):
-            o = own.get(name)
-            if o is None:
-                o = own[name] = owner_list[tasks[name]["data"]["peer"]]
-            return o
-
-        def level(name):
-            l = level_of.get(name)
-            if l is not None:
-                return l
-            stack = [name]
-            while stack:
-                n = stack[-1]
-                ins = tasks[n]["inputs"]
-                if not ins:
-                    level_of[n] = 0
-                    stack.pop()
-                    continue
-                missing = [i[0] for i in ins if i[0] not in level_of]
-                if missing:
-                    stack.extend(missing)
-                    continue
-                level_of[n] = 1 + max(level_of[i[0]] for i in ins)
-                stack.pop()
-            return level_of[name]
-
-        mine = [name for name, t in tasks.items() if owner_list[t["data"]["peer"]] == me]
-        for name in mine:
-            own[name] = me
-        xchg_own = set()
-        remote = {}                               # level -> [(consumer rank, my value consumed there)], one per edge
-        for name in mine:
-            t = tasks[name]
-            l = level(name)
-            if t["inputs"] and [1 for i in t["inputs"] if owner(i[0]) != me]:     # (every input's owner gets memoised)
-                if t["func"] != "aggregate":
-                    raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % name)
-                xchg_own.add(l)
-            for cons, idx in t["outputs"]:
-                q = owner(cons)
-                if q != me:
-                    if tasks[cons]["func"] != "aggregate":
-                        raise RuntimeError("task %s consumes a model of another GPU's node outside an aggregate" % cons)
-                    lc = level(cons)
-                    remote.setdefault(lc, []).append((q, (name, idx)))
-                    xchg_own.add(lc)
-        n_slots = self.LEVEL_SLOTS
-        mask = torch.zeros(n_slots + 1, dtype=torch.uint8)
-        for l in xchg_own:
-            mask[min(l, n_slots)] = 1             # slot n_slots = "deeper than the bitmap"
-        dist.all_reduce(mask, op=dist.ReduceOp.MAX, group=side)
-        if int(mask[n_slots]):
-            return self._levelise_global()        # every rank sees the flag and takes the same path
-        self._task_owner = own
-        self._level_of = level_of
-        self._remote = remote
-        self._xchg_levels = set(torch.nonzero(mask[:n_slots]).flatten().tolist())
-        self._xchg_index = {l: i for i, l in enumerate(sorted(self._xchg_levels))}
-        if self.transport == "push":
-            self._remote_index = [None] * self.world
-            counts = np.bincount(self.owner_of, minlength=self.world)
-            self._n_remote = [int(len(self.owner_of) - c) for c in counts]
-        n_levels = max((level_of[n] for n in mine), default=-1) + 1
-        n_levels = max(n_levels, max(self._xchg_levels, default=-1) + 1)
-        out = [[] for _ in range(n_levels)]
-        for n in mine:
-            out[level_of[n]].append(n)
-        return out
-
-    def _levelise_global(self):
         tasks, me = self.tasks, self.rank
         owner_list = self.owner_of.tolist()       # plain ints: numpy scalar indexing is ~10x slower per lookup
         own: Dict[str, int] = {}

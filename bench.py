@@ -101,7 +101,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -118,9 +118,13 @@ class ClockSampler:
         time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
-        for ts, l in self.lines:
-            if t0 is not None and not (t0 <= ts <= (t1 + 0.2)):
-                continue
+        lines, window = self.lines, "timed region"
+        if t0 is not None:
+            lines = [(ts, l) for ts, l in self.lines if t0 <= ts <= t1 + 0.2]
+            if not lines:                          # a timed region shorter than the sampling period: the samples
+                lines = [(ts, l) for ts, l in self.lines if t0 - 0.5 <= ts <= t1 + 0.5]    # around it (warm-up load)
+                window = "no sample inside the timed region; +-0.5 s around it"
+        for ts, l in lines:
             f = [x.strip() for x in l.split(",")]
             if len(f) < 9:
                 continue
@@ -132,7 +136,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -698,7 +702,7 @@ def main():
     P, W, Ksteps = m["P"], args.warmup, args.steps
     job = Job(args, n_nodes, world, rank, dev, dist)
     pk = peaks()
-    leg = device_leg(job, W, Ksteps, ClockSampler(local_rank))
+    leg = device_leg(job, W, Ksteps, ClockSampler(local_rank) if job.rank == 0 else None)
     total_ms = leg["total_ms"]
     per_gpu = job.n_local
     agg_bytes = 2 * per_gpu * P * 4                                   # per GPU per launch

@@ -59,7 +59,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C2 (256-node) secondary line at N=1")
     ap.add_argument("--model", default="gnlenet", choices=["gnlenet", "femnist"],
-                    help="gnlenet = the metric's model (default); femnist = the C3 model (fp32 path)")
+                    help="gnlenet = the metric's model (default); femnist = the C3 model")
     a = ap.parse_args()
     if a.nodes and a.nodes_per_gpu:
         ap.error("--nodes and --nodes-per-gpu are exclusive")
@@ -336,7 +336,7 @@ def workload_config(n_nodes, k, args, world):
                   % (2 * per_gpu * m["P"] * 4 // 1000000) if args.mode == "round" else
                   "inputs larger than L2: X + Y = %d MB per GPU; the pool alternates between two row sets"
                   % (2 * per_gpu * m["P"] * 4 // 1000000),
-            "train_math": "fp32 CUDA cores" if (args.precision == 0 or args.model == "femnist")
+            "train_math": "fp32 CUDA cores" if args.precision == 0 else "conv2 on bf16 tcgen05 tensor cores (fp32 accumulate), the rest fp32 CUDA cores" if args.model == "femnist"
             else "bf16 tcgen05 tensor cores, fp32 accumulate",
             "dataset_residency": "node partitions uploaded once (like the reference's cached partitions); "
                                  "e2e uploads per-round task descriptors + minibatch index"}
@@ -382,7 +382,7 @@ class Job:
                                   model=None if args.model == "femnist" else "gnlenet",
                                   data_dir=os.path.join(REPO, "gpurun_out", "bench_data"),
                                   learning=LearningSettings(m["lr"], m["mu"], 0.0, BATCH, LOCAL_STEPS), k=self.k,
-                                  precision=0 if args.model == "femnist" else args.precision)
+                                  precision=args.precision)
         if world > 1:
             from dls_b200.partition import block_partition, partition_nodes
             # exponential graph: contiguous blocks (edges i -> i + 2^j); else grow parts inside the topology
@@ -739,14 +739,14 @@ def main():
     leg["solver"].finish()
     e2e = e2e_leg(job, W, Ksteps)
     e2e_value = node_steps_per_round / (e2e["ms_per_step"] / 1e3)
-    math_label = "fp32 CUDA cores" if (args.precision == 0 or args.model == "femnist") else "bf16 tcgen05"
+    math_label = "fp32 CUDA cores" if args.precision == 0 else "bf16 tcgen05"
 
     if rank == 0:
         line = {
             "metric": "node-train-steps/sec", "value": value, "unit": "node-train-steps/s", "n_gpus": world,
             "steps": Ksteps, "warmup": W, "ms_per_step": total_ms / Ksteps, "higher_is_better": True,
             "scaling": scaling, "vs_baseline": None,
-            "dtype": "f32" if (args.precision == 0 or args.model == "femnist") else "bf16",
+            "dtype": "f32" if args.precision == 0 else "bf16",
             "data": "synthetic", "config": workload_config(n_nodes, job.k, args, world),
             # the dominant kernel group: all kernels of the train wave (99 % of the step)
             "roofline": {"kernel": "train wave (all kernels of %d local steps x %d nodes per GPU)" % (LOCAL_STEPS, per_gpu),

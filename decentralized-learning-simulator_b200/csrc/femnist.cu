@@ -1,4 +1,6 @@
-// FEMNIST CNN train / eval waves (fp32 CUDA-core path).
+// FEMNIST CNN train / eval waves.  precision 0: fp32 CUDA cores throughout.  precision 1: conv2 (94 % of the
+// FLOPs) forward / data gradient / weight gradient on tensor cores (tc_conv.cu: bf16 operands, fp32 accumulate),
+// fed with bf16 channel-chunk planes that conv1 and the pool backward write; everything else fp32.
 //
 // Architecture (reference: dasklearn/models/femnist.py:45-85; the reference itself cannot import
 // this model — its dataset module is missing — so parity is against the CPU restatement in
@@ -11,6 +13,7 @@
 // forward, the data gradient, the weight gradient and the optimizer update.
 #include "gnlenet.cuh"
 #include "conv_simt.cuh"
+#include "tc_common.cuh"
 #include <math.h>
 
 namespace dls {
@@ -34,7 +37,12 @@ struct Ws {
     float *prep, *glog, *G;
     int64_t ldg;
     int32_t *desc_i32;
+    // precision 1: bf16 planes [slot][C/8][RUNP14][8] (pixel r = y * 16 + x, gap pixels zero) + bf16 weight copies
+    uint16_t *a1p, *dc2p, *zplane;
+    void *prep_tc;
+    int tc;
 };
+constexpr int A1P_SZ = 4 * gnl::RUNP14 * 8, DC2P_SZ = 8 * gnl::RUNP14 * 8;      // bf16 elements per sample
 
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 struct Carver {
@@ -51,6 +59,11 @@ static int64_t carve(Ws &ws, void *base, int n_groups, int gs, int n_models, boo
 {
     Carver c{reinterpret_cast<char *>(base), 0};
     const int64_t S = (int64_t)n_groups * gs;
+    ws.tc = 0;
+    ws.a1p = c.take<uint16_t>(S * A1P_SZ);               // sized for either precision
+    ws.prep_tc = c.take<uint16_t>((int64_t)n_models * gnl::TC_PREP_ELEMS);
+    ws.zplane = c.take<uint16_t>(gnl::RUNP15 * 8);
+    ws.dc2p = backward ? c.take<uint16_t>(S * DC2P_SZ) : nullptr;
     ws.a1 = c.take<float>(S * A1_SZ);
     ws.c2 = c.take<float>(S * C2_SZ);
     ws.a2 = c.take<float>(S * A2_SZ);
@@ -136,6 +149,14 @@ conv1_relu_pool_kernel(Pass p, Ws ws, int save_bwd)
         }
         ws.a1[(int64_t)slot * A1_SZ + o] = best;
         if (save_bwd) ws.idx1[(int64_t)slot * A1_SZ + o] = (uint8_t)bi;
+        if (ws.tc)
+            reinterpret_cast<__nv_bfloat16 *>(ws.a1p)[(int64_t)slot * A1P_SZ + ((co >> 3) * gnl::RUNP14 + py * 16 + px) * 8 +
+                                                      (co & 7)] = __float2bfloat16_rn(best);
+    }
+    if (ws.tc && t < 4 * 26) {                           // the two gap pixels after rows 0..12 of every plane
+        const int pl = t / 26, r = t - pl * 26;
+        reinterpret_cast<uint4 *>(ws.a1p + (int64_t)slot * A1P_SZ)[pl * gnl::RUNP14 + (r >> 1) * 16 + 14 + (r & 1)] =
+            make_uint4(0u, 0u, 0u, 0u);
     }
 }
 
@@ -146,13 +167,16 @@ relu_pool2_kernel(Pass p, Ws ws, int save_bwd)
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
     const float *src = ws.c2 + (int64_t)slot * C2_SZ;
+    int m;
+    const float *row = model_row(p, slot / p.gs, m);
     for (int o = t; o < A2_SZ; o += 256) {
         const int c = o & 63, pp = o >> 6, py = pp / 7, px = pp - py * 7;
+        const float bias = ws.tc ? row[OFF_B2 + c] : 0.f;   // the tensor-core convolution leaves the bias to its consumer
         float best = -INFINITY;
         int bi = 0;
 #pragma unroll
         for (int d = 0; d < 4; ++d) {
-            float v = src[((2 * py + (d >> 1)) * 14 + 2 * px + (d & 1)) * 64 + c];
+            float v = src[((2 * py + (d >> 1)) * 14 + 2 * px + (d & 1)) * 64 + c] + bias;
             v = v > 0.f ? v : 0.f;
             if (v > best) { best = v; bi = d; }
         }
@@ -375,6 +399,26 @@ pool2_bwd_kernel(Pass p, Ws ws)
 {
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
+    if (ws.tc) {
+        // bf16 planes: one 16-byte entry (8 channels of a pixel) per item, gap pixels zeroed
+        uint4 *dst = reinterpret_cast<uint4 *>(ws.dc2p + (int64_t)slot * DC2P_SZ);
+        for (int i = t; i < 196 * 8; i += 256) {
+            const int ch = i / 196, pix = i - ch * 196, y = pix / 14, x = pix - y * 14;
+            const int sel = (y & 1) * 2 + (x & 1);
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int64_t b = (int64_t)slot * A2_SZ + (ch * 8 + e) * 49 + (y >> 1) * 7 + (x >> 1);
+                v[e] = ((int)ws.idx2[b] == sel && ws.a2[b] > 0.f) ? ws.da2[b] : 0.f;
+            }
+            dst[ch * gnl::RUNP14 + y * 16 + x] = tc::pack8_bf16(v);
+        }
+        for (int i = t; i < 8 * 26; i += 256) {
+            const int pl = i / 26, r = i - pl * 26;
+            dst[pl * gnl::RUNP14 + (r >> 1) * 16 + 14 + (r & 1)] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        return;
+    }
     for (int e = t; e < C2_SZ; e += 256) {
         const int c = e & 63, pix = e >> 6, y = pix / 14, x = pix - y * 14;
         const int o = c * 49 + (y >> 1) * 7 + (x >> 1);
@@ -382,6 +426,34 @@ pool2_bwd_kernel(Pass p, Ws ws)
         const bool hit = (int)ws.idx2[b] == ((y & 1) * 2 + (x & 1)) && ws.a2[b] > 0.f;
         ws.dc2[(int64_t)slot * C2_SZ + e] = hit ? ws.da2[b] : 0.f;
     }
+}
+
+// conv2 bias gradient (tensor-core path): every pooled position routes its gradient to exactly one conv2 pixel, so
+// db2[c] = sum over samples and pooled positions of da2 where the pooled activation is positive.  One CTA per node,
+// samples in slot order (deterministic).
+__global__ void __launch_bounds__(256)
+bias2_grad_kernel(Pass p, Ws ws)
+{
+    __shared__ float sm[A2_SZ];
+    const int g = blockIdx.x, t = threadIdx.x;
+    if (p.gcount[g] <= 0) return;
+    float acc = 0.f;
+    for (int s = 0; s < p.gs; ++s) {
+        const int slot = g * p.gs + s;
+        if (p.img_idx[slot] < 0) continue;
+        __syncthreads();
+        for (int i = t; i < A2_SZ; i += 256) {
+            const int64_t b = (int64_t)slot * A2_SZ + i;
+            sm[i] = ws.a2[b] > 0.f ? ws.da2[b] : 0.f;
+        }
+        __syncthreads();
+        if (t < 64) {
+            float a = 0.f;
+            for (int k = 0; k < 49; ++k) a += sm[t * 49 + k];
+            acc += a;
+        }
+    }
+    if (t < 64) ws.G[(int64_t)g * ws.ldg + OFF_B2 + t] = acc;
 }
 
 // conv1 weight/bias gradient: the gradient reaches conv1 only at the arg-max of each 2x2 window and
@@ -452,10 +524,15 @@ static int forward(const Pass &p, Ws &ws, bool save, cudaStream_t st)
     const int S = p.n_groups * p.gs, sv = save ? 1 : 0;
     prep_kernel<<<dim3(8, p.n_models), 256, 0, st>>>(p, ws.prep, p.gmodel ? nullptr : p.gcount);
     DLS_LAUNCH_CHECK();
+    if (ws.tc && (rc = gnl::fem_prep_conv2_tc(p, ws.prep_tc, OFF_W2, save, st))) return rc;
     conv1_relu_pool_kernel<<<S, 256, 0, st>>>(p, ws, sv);
     DLS_LAUNCH_CHECK();
-    gnl::conv5_kernel<32, 64, 14, true><<<S, 256, 18 * 18 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PREP_STRIDE, PO_W2T, OFF_B2);
-    DLS_LAUNCH_CHECK();
+    if (ws.tc) {
+        if ((rc = gnl::fem_conv2_fwd_tc(p, ws.a1p, ws.c2, ws.prep_tc, st))) return rc;
+    } else {
+        gnl::conv5_kernel<32, 64, 14, true><<<S, 256, 18 * 18 * 32 * 4, st>>>(ws.a1, ws.c2, p, ws.prep, PREP_STRIDE, PO_W2T, OFF_B2);
+        DLS_LAUNCH_CHECK();
+    }
     relu_pool2_kernel<<<S, 256, 0, st>>>(p, ws, sv);
     DLS_LAUNCH_CHECK();
     dense_fwd_kernel<FEAT, HID, true><<<dim3(p.n_groups, HID / 32), 256, 0, st>>>(ws.a2, ws.h1, HID, p, OFF_FC1W, OFF_FC1B);
@@ -478,12 +555,22 @@ static int backward(const Pass &p, Ws &ws, cudaStream_t st)
     DLS_LAUNCH_CHECK();
     pool2_bwd_kernel<<<S, 256, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
-    gnl::Workspace gw;                     // the shared conv kernels only use the gradient-row fields
-    gw.G = ws.G; gw.ldg = ws.ldg;
-    gnl::conv_wgrad_kernel<64, 14><<<dim3(p.n_groups, 4), 256, (18 * 18 * 32 + 196 * 16) * 4, st>>>(ws.a1, ws.dc2, p, gw, OFF_W2, OFF_B2);
-    DLS_LAUNCH_CHECK();
-    gnl::conv5_kernel<64, 32, 14, false><<<S, 256, 18 * 18 * 64 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PREP_STRIDE, PO_W2D, 0);
-    DLS_LAUNCH_CHECK();
+    if (ws.tc) {
+        int rc;
+        cudaError_t e = cudaMemsetAsync(ws.zplane, 0, gnl::RUNP15 * 16, st);
+        if (e != cudaSuccess) return (int)e;
+        bias2_grad_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
+        DLS_LAUNCH_CHECK();
+        if ((rc = gnl::fem_conv2_wgrad_tc(p, ws.a1p, ws.dc2p, ws.zplane, ws.G, ws.ldg, OFF_W2, st))) return rc;
+        if ((rc = gnl::fem_conv2_dgrad_tc(p, ws.dc2p, ws.da1, ws.prep_tc, st))) return rc;
+    } else {
+        gnl::Workspace gw{};                   // the shared conv kernels only use the gradient-row fields
+        gw.G = ws.G; gw.ldg = ws.ldg;
+        gnl::conv_wgrad_kernel<64, 14><<<dim3(p.n_groups, 4), 256, (18 * 18 * 32 + 196 * 16) * 4, st>>>(ws.a1, ws.dc2, p, gw, OFF_W2, OFF_B2);
+        DLS_LAUNCH_CHECK();
+        gnl::conv5_kernel<64, 32, 14, false><<<S, 256, 18 * 18 * 64 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PREP_STRIDE, PO_W2D, 0);
+        DLS_LAUNCH_CHECK();
+    }
     conv1_wgrad_kernel<<<dim3(p.n_groups, 4), 256, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     return 0;
@@ -496,10 +583,11 @@ int64_t train_workspace_bytes(int n_tasks, int batch, bool own_G)
 }
 
 int step(const Pass &p, void *workspace, float *G, int64_t ldg, float *loss_out, float **G_used, int64_t *ldg_used,
-         cudaStream_t st)
+         int precision, cudaStream_t st)
 {
     Ws ws;
     carve(ws, workspace, p.n_groups, p.gs, p.n_models, true, G == nullptr);
+    ws.tc = precision == 1;
     if (G) { ws.G = G; ws.ldg = ldg; }
     int rc;
     if ((rc = forward(p, ws, true, st))) return rc;
@@ -548,13 +636,14 @@ int64_t eval_workspace_bytes(int n_models, int n_test)
 
 int eval(const float *X, int64_t ldx, const int32_t *model_rows, int n_models, const uint8_t *test_images,
          const int64_t *test_labels, int n_test, int32_t *out_correct, double *out_loss_sum, float *out_logits,
-         void *workspace, cudaStream_t st)
+         int precision, void *workspace, cudaStream_t st)
 {
     const int gpm = (n_test + EVAL_GS - 1) / EVAL_GS;
     const int64_t total = (int64_t)n_models * gpm;
     const int chunk = (int)(total < EVAL_CHUNK_GROUPS ? total : EVAL_CHUNK_GROUPS);
     Ws ws;
     const int64_t used = carve(ws, workspace, chunk, EVAL_GS, n_models, false, false);
+    ws.tc = precision == 1;
     float *glog_all = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + used);
     int32_t *d_img_idx = ws.desc_i32, *d_gmodel = ws.desc_i32 + (int64_t)chunk * EVAL_GS, *d_gcount = d_gmodel + chunk;
     Pass p;

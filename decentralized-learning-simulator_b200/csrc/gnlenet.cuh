@@ -30,6 +30,8 @@ constexpr int GNP_SZ = 3 * (C1 + C2 + C3);   // per-slot partials: GN gamma, GN 
 // bf16 plane runs (tensor-core path): RUN = (H-1)*(H+2) + H pixels, padded to a multiple of 8
 constexpr int RUN15 = 14 * 17 + 15, RUNP15 = 256;     // 15x15 maps (a1, dc2): 253 pixels, plane = 4096 B
 constexpr int RUN7 = 6 * 9 + 7, RUNP7 = 64;           // 7x7 maps (a2, dc3): 61 pixels, plane = 1024 B
+constexpr int RUN14 = 13 * 16 + 14, RUNP14 = 224;     // 14x14 maps (FEMNIST a1, dc2): 222 pixels
+__host__ __device__ constexpr int plane_runp(int h) { return h == 15 ? RUNP15 : (h == 14 ? RUNP14 : RUNP7); }
 constexpr int A1P_SZ = 4 * RUNP15 * 8, A2P_SZ = 4 * RUNP7 * 8, DC2P_SZ = 4 * RUNP15 * 8, DC3P_SZ = 8 * RUNP7 * 8;   // bf16 elements per sample
 
 constexpr int W2T_SZ = 25 * 32 * 32, W3T_SZ = 25 * 32 * 64;
@@ -104,6 +106,14 @@ int prep_w1_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv1_fwd_tc(const Pass &p, Workspace &ws, bool save, cudaStream_t st);
 int conv1_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
 int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st);
+
+// FEMNIST conv2 (32 -> 64 channels, 14x14 maps) on the same kernels (tc_conv.cu).  `prep_tc`: [n_models][TC_PREP_ELEMS]
+// bf16 (only the 32->64 slots are used); planes: [slot][C/8][RUNP14][8] bf16; c2 / da1: fp32 NHWC, no bias added.
+int fem_prep_conv2_tc(const Pass &p, void *prep_tc, int w_off, bool backward, cudaStream_t st);
+int fem_conv2_fwd_tc(const Pass &p, const uint16_t *a1p, float *c2, const void *prep_tc, cudaStream_t st);
+int fem_conv2_dgrad_tc(const Pass &p, const uint16_t *dc2p, float *da1, const void *prep_tc, cudaStream_t st);
+int fem_conv2_wgrad_tc(const Pass &p, const uint16_t *a1p, const uint16_t *dc2p, const uint16_t *zeros, float *G,
+                       int64_t ldg, int w_off, cudaStream_t st);
 
 int prep_weights(const Pass &p, Workspace &ws, bool backward, cudaStream_t st);
 int forward(const Pass &p, Workspace &ws, bool save_for_backward, cudaStream_t st);

@@ -50,14 +50,15 @@ __device__ __forceinline__ int64_t grouped_entry(int tap, int chunk, int nck, in
 }
 
 __global__ void __launch_bounds__(256)
-prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t *model_active, int grouped)
+prep_weights_tc_kernel(Pass p, __nv_bfloat16 *prep, int backward, const int32_t *model_active, int grouped,
+                       int part0, int off_w2, int off_w3)
 {
     extern __shared__ __align__(16) float wsrc[];                 // [16][PREP_ROW]
-    const int m = blockIdx.y, part = blockIdx.x, t = threadIdx.x;
+    const int m = blockIdx.y, part = part0 + blockIdx.x, t = threadIdx.x;
     if (model_active && model_active[m] == 0) return;
     const bool l3 = part >= 2;
     const int co0 = (l3 ? part - 2 : part) * 16, nco = l3 ? 64 : 32;
-    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx + (l3 ? OFF_W3 : OFF_W2) + co0 * 800;
+    const float *row = p.X + (int64_t)p.mrow[m] * p.ldx + (l3 ? off_w3 : off_w2) + co0 * 800;
     __nv_bfloat16 *dst_u = prep + (int64_t)m * TC_PREP_ELEMS + (l3 ? TCO_W3U : TCO_W2U);
     __nv_bfloat16 *dst_d = prep + (int64_t)m * TC_PREP_ELEMS + (l3 ? TCO_W3UD : TCO_W2UD);
     for (int i = t; i < 16 * 200; i += 256) {                     // 16 rows of 800 floats, float4 loads
@@ -347,7 +348,7 @@ struct ConvTc3Cfg : ConvTcCfg<CIN, COUT, H, SB> {
     static constexpr int RING_FLOATS = RING * 4 * NCG * RQ;
     static constexpr int SMEM = Base::B_BYTES + NST * Base::A_BYTES + RING_FLOATS * 4 + 320;
     static constexpr int RUN = Base::NORIG;                            // pixels of a sample's plane run
-    static constexpr int RUNP = H == 15 ? RUNP15 : RUNP7;              // plane stride (pixels) in global memory
+    static constexpr int RUNP = plane_runp(H);                         // plane stride (pixels) in global memory
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
     static_assert(Base::TPS * 128 >= Base::NORIG + 1 || !Base::PER_SAMPLE, "last valid origin needs its neighbour in the tile");
     static_assert(Base::TILES_GLOBAL * 128 >= (SB - 1) * Base::NPS + Base::NORIG + 1 || Base::PER_SAMPLE,
@@ -629,7 +630,7 @@ conv_tc3_kernel(const float *__restrict__ in, const uint16_t *__restrict__ in_pl
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-template <int CIN, int COUT, int H, int SB, bool BIAS>
+template <int CIN, int COUT, int H, int SB, bool BIAS, int NSTP = 3>
 static int launch_conv_tc(const float *in, const uint16_t *in_planes, float *out, const Pass &p, const __nv_bfloat16 *wprep,
                           int wprep_off, int bias_off, cudaStream_t st)
 {
@@ -640,7 +641,7 @@ static int launch_conv_tc(const float *in, const uint16_t *in_planes, float *out
     const int parts = (p.gs + spc - 1) / spc;
     if (!tune_value(TUNE_CONV_UNGROUPED)) {
         if (in_planes) {
-            constexpr int NST = 3;
+            constexpr int NST = NSTP;
             using C3 = ConvTc3Cfg<CIN, COUT, H, SB, NST>;
             static PerDeviceOnce attr3p;
             int rc3 = ensure_dyn_smem(conv_tc3_kernel<CIN, COUT, H, SB, true, NST>, C3::SMEM, attr3p);
@@ -676,7 +677,7 @@ int prep_weights_tc(const Pass &p, Workspace &ws, bool backward, cudaStream_t st
     dim3 grid(6, p.n_models);
     const int32_t *active = p.gmodel ? nullptr : p.gcount;
     prep_weights_tc_kernel<<<grid, 256, PREP_SMEM, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(ws.prep_tc), backward ? 1 : 0,
-                                                 active, tune_value(TUNE_CONV_UNGROUPED) ? 0 : 1);
+                                                 active, tune_value(TUNE_CONV_UNGROUPED) ? 0 : 1, 0, OFF_W2, OFF_W3);
     DLS_LAUNCH_CHECK();
     if (ws.zplane) {                              // a plane run of zeros (dY of the missing samples of a partial chunk)
         cudaError_t e = cudaMemsetAsync(ws.zplane, 0, RUNP15 * 16, st);
@@ -807,7 +808,7 @@ conv_wgrad_tc_kernel(const float *__restrict__ in, const float *__restrict__ dY,
     if (PLANES && warp >= 1) {
         // ------------------------------ producer: bulk copies ------------------------------
         if (warp == 1 && tc::elect_one()) {
-            constexpr int RUN = C::G::NORIG, RUNP = H == 15 ? RUNP15 : RUNP7, NCOPY = QUAD ? 4 : (PAIR ? 2 : 1);
+            constexpr int RUN = C::G::NORIG, RUNP = plane_runp(H), NCOPY = QUAD ? 4 : (PAIR ? 2 : 1);
             constexpr uint32_t TX = (uint32_t)(SB * ((COUT / 8) * NCOPY + 4 * NIC) * RUN * 16);
             for (int c = 0; c < n_chunks; ++c) {
                 const int b = c & 1;
@@ -1042,6 +1043,42 @@ int conv3_wgrad_tc(const Pass &p, Workspace &ws, cudaStream_t st)
 {
     const bool pl = !tune_value(TUNE_CONV_UNGROUPED);
     return launch_wgrad_tc<64, 7, 2, true>(ws.a2, ws.dc3, pl ? ws.a2p : nullptr, pl ? ws.dc3p : nullptr, p, ws, OFF_W3, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// FEMNIST conv2 (32 -> 64, 14x14): the weight tensor has the shape of GNLeNet's conv3, so the bf16 copies use
+// the same slots of the prep record; two M = 128 tiles per sample (222 origins).
+// ------------------------------------------------------------------------------------------
+int fem_prep_conv2_tc(const Pass &p, void *prep_tc, int w_off, bool backward, cudaStream_t st)
+{
+    static PerDeviceOnce attr;
+    int rc = ensure_dyn_smem(prep_weights_tc_kernel, PREP_SMEM, attr);
+    if (rc) return rc;
+    const int32_t *active = p.gmodel ? nullptr : p.gcount;
+    prep_weights_tc_kernel<<<dim3(4, p.n_models), 256, PREP_SMEM, st>>>(p, reinterpret_cast<__nv_bfloat16 *>(prep_tc),
+                                                                     backward ? 1 : 0, active, 1, 2, 0, w_off);
+    DLS_LAUNCH_CHECK();
+    return 0;
+}
+int fem_conv2_fwd_tc(const Pass &p, const uint16_t *a1p, float *c2, const void *prep_tc, cudaStream_t st)
+{
+    if (!a1p || tune_value(TUNE_CONV_UNGROUPED)) return DLS_E_ARG;
+    return launch_conv_tc<32, 64, 14, 1, false, 3>(nullptr, a1p, c2, p, reinterpret_cast<const __nv_bfloat16 *>(prep_tc),
+                                                   TCO_W3U, 0, st);
+}
+int fem_conv2_dgrad_tc(const Pass &p, const uint16_t *dc2p, float *da1, const void *prep_tc, cudaStream_t st)
+{
+    if (!dc2p || tune_value(TUNE_CONV_UNGROUPED)) return DLS_E_ARG;
+    return launch_conv_tc<64, 32, 14, 1, false, 2>(nullptr, dc2p, da1, p, reinterpret_cast<const __nv_bfloat16 *>(prep_tc),
+                                                   TCO_W3UD, 0, st);
+}
+int fem_conv2_wgrad_tc(const Pass &p, const uint16_t *a1p, const uint16_t *dc2p, const uint16_t *zeros, float *G,
+                       int64_t ldg, int w_off, cudaStream_t st)
+{
+    if (!a1p || !dc2p || !zeros) return DLS_E_ARG;
+    Workspace w{};
+    w.G = G; w.ldg = ldg; w.zplane = const_cast<uint16_t *>(zeros);
+    return launch_wgrad_tc<64, 14, 1, true>(nullptr, nullptr, a1p, dc2p, p, w, w_off, st);
 }
 
 }  // namespace gnl

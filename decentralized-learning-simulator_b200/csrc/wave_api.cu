@@ -5,11 +5,11 @@ namespace dls {
 namespace fem {
 int64_t train_workspace_bytes(int n_tasks, int batch, bool own_G);
 int step(const gnl::Pass &p, void *workspace, float *G, int64_t ldg, float *loss_out, float **G_used,
-         int64_t *ldg_used, cudaStream_t st);
+         int64_t *ldg_used, int precision, cudaStream_t st);
 int64_t eval_workspace_bytes(int n_models, int n_test);
 int eval(const float *X, int64_t ldx, const int32_t *model_rows, int n_models, const uint8_t *test_images,
          const int64_t *test_labels, int n_test, int32_t *out_correct, double *out_loss_sum, float *out_logits,
-         void *workspace, cudaStream_t st);
+         int precision, void *workspace, cudaStream_t st);
 }  // namespace fem
 
 // Fused optimizer update over the wave's rows — torch.optim.SGD semantics
@@ -170,7 +170,7 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
     if (arch != DLS_ARCH_GNLENET && arch != DLS_ARCH_FEMNIST) return DLS_E_SHAPE;
     if (precision != 0 && precision != 1) return DLS_E_SHAPE;
     if (arch == DLS_ARCH_FEMNIST) {
-        // FEMNIST CNN: fp32 CUDA-core kernels only (precision is ignored)
+        // FEMNIST CNN: precision 1 runs conv2 on tensor cores (femnist.cu)
         if (!task_row || !task_peer || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0 ||
             n_steps < 0)
             return DLS_E_ARG;
@@ -192,7 +192,7 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
             float *G = nullptr;
             int64_t ldg = 0;
             if ((rcf = fem::step(p, workspace, nullptr, 0, loss_out ? loss_out + (int64_t)s * n_tasks : nullptr, &G,
-                                 &ldg, stf)))
+                                 &ldg, precision, stf)))
                 return rcf;
             dim3 grid(128, n_tasks);
             sgd_update_kernel<<<grid, 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
@@ -307,7 +307,7 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
         gnl::Pass p;
         p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks; p.gmodel = nullptr; p.mrow = task_row;
         p.img_idx = mb_index; p.gcount = mb_count; p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
-        return fem::step(p, workspace, G, ldg, loss_out, nullptr, nullptr, (cudaStream_t)stream);
+        return fem::step(p, workspace, G, ldg, loss_out, nullptr, nullptr, precision, (cudaStream_t)stream);
     }
     if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0)
         return DLS_E_ARG;
@@ -355,7 +355,7 @@ extern "C" int dls_eval_wave(int32_t arch, const float *X, int64_t ldx, const in
         if (n_models == 0 || n_test == 0) return 0;
         if (workspace_bytes < fem::eval_workspace_bytes(n_models, n_test)) return DLS_E_WS;
         return fem::eval(X, ldx, model_rows, n_models, test_images, test_labels, n_test, out_correct, out_loss_sum,
-                         out_logits, workspace, (cudaStream_t)stream);
+                         out_logits, precision, workspace, (cudaStream_t)stream);
     }
     if (!model_rows || !test_images || !test_labels || !out_correct || !out_loss_sum || !workspace ||
         n_models < 0 || n_test < 0)

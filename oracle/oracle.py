@@ -162,6 +162,16 @@ def femnist_forward(p, x):
     return F.linear(x, p["fc2.weight"], p["fc2.bias"])
 
 
+def femnist_forward_bf16(p, x):
+    """FEMNIST CNN with conv2 evaluated like the precision-1 kernels (bf16 operands, fp32 accumulate, forward /
+    data gradient / weight gradient alike); conv1 and the dense layers stay fp32."""
+    x = F.max_pool2d(F.relu(F.conv2d(x, p["conv1.weight"], p["conv1.bias"], padding=2)), 2, 2)
+    x = F.max_pool2d(F.relu(_ConvBf16.apply(x, p["conv2.weight"], p["conv2.bias"], True)), 2, 2)
+    x = torch.flatten(x, 1)
+    x = F.relu(F.linear(x, p["fc1.weight"], p["fc1.bias"]))
+    return F.linear(x, p["fc2.weight"], p["fc2.bias"])
+
+
 def to_tensor(images_u8: np.ndarray) -> torch.Tensor:
     """torchvision ToTensor + default_collate (dasklearn/datasets/transforms.py:9,16-18):
     uint8 HWC -> contiguous fp32 CHW / 255."""
@@ -236,7 +246,9 @@ def gradient_of(layout, row: np.ndarray, images_u8: np.ndarray, labels: np.ndarr
     `emulate_bf16`: evaluate conv2/conv3 with bf16-rounded operands like the precision-1 kernels."""
     P = layout.P
     wl = torch.from_numpy(np.array(row[:P], dtype=np.float32, copy=True)).requires_grad_(True)
-    if emulate_bf16:
+    if emulate_bf16 and layout.name != "gnlenet":
+        out = femnist_forward_bf16(_views(layout, wl), to_tensor(images_u8))
+    elif emulate_bf16:
         out = gnlenet_forward_bf16(_views(layout, wl), to_tensor(images_u8), wgrad_bf16, conv1_wgrad_bf16)
     else:
         out = forward(layout, wl, to_tensor(images_u8))

@@ -43,24 +43,29 @@ def test_layout_and_init():
     assert np.array_equal(initial_row(L, 42).numpy(), O.initial_row(L, 42))
 
 
-def test_eval(cuda):
+@pytest.mark.parametrize("precision", [0, 1])
+def test_eval(cuda, precision):
     timg, tlab = synthetic.make_test_split(100, 28, 1, 62)
     X = rows(2)
     Xd = torch.from_numpy(X).to(cuda)
     logits = torch.zeros((2, 100, 62), device=cuda)
     correct, loss = K.eval_wave(L, Xd, torch.tensor([1, 0], dtype=torch.int32, device=cuda),
                                 torch.from_numpy(timg.reshape(100, -1)).to(cuda), torch.from_numpy(tlab).to(cuda),
-                                K.Workspace(cuda), out_logits=logits)
+                                K.Workspace(cuda), out_logits=logits, precision=precision)
     torch.cuda.synchronize()
     for j, r in enumerate([1, 0]):
         ref = O.logits(L, X[r], timg)
-        assert np.abs(logits[j].cpu().numpy() - ref).max() < 2e-4
+        assert np.abs(logits[j].cpu().numpy() - ref).max() < (5e-3 if precision else 2e-4)
         acc, l, nc = O.evaluate(L, X[r], timg, tlab)
-        assert abs(int(correct[j]) - nc) <= 1 and abs(float(loss[j]) / 100 - l) < 1e-4
+        assert abs(int(correct[j]) - nc) <= (3 if precision else 1)
+        assert abs(float(loss[j]) / 100 - l) < (2e-3 if precision else 1e-4)
 
 
+# precision 1 = conv2 on bf16 tensor cores (fp32 accumulate): the fp32 autograd oracle is matched to bf16 rounding
+# (2^-9 relative per operand), the fp32 path to summation-order noise.
+@pytest.mark.parametrize("precision", [0, 1])
 @pytest.mark.parametrize("batch,counts", [(32, [32, 16, 1]), (8, [8, 0, 5])])
-def test_gradient_vs_autograd(cuda, data, batch, counts):
+def test_gradient_vs_autograd(cuda, data, batch, counts, precision):
     imgs, labs = data
     n = len(counts)
     X = rows(n, seed=1)
@@ -74,7 +79,7 @@ def test_gradient_vs_autograd(cuda, data, batch, counts):
     K.grad_wave(L, Xd, G, torch.arange(n, dtype=torch.int32, device=cuda),
                 torch.from_numpy(imgs.reshape(-1, 784)).to(cuda), torch.from_numpy(labs.reshape(-1)).to(cuda),
                 torch.from_numpy(idx).to(cuda), torch.tensor(counts, dtype=torch.int32, device=cuda), batch,
-                K.Workspace(cuda), loss_out=loss)
+                K.Workspace(cuda), loss_out=loss, precision=precision)
     torch.cuda.synchronize()
     Gh = G.cpu().numpy()
     fi, fl = imgs.reshape(-1, 28, 28, 1), labs.reshape(-1)
@@ -83,14 +88,24 @@ def test_gradient_vs_autograd(cuda, data, batch, counts):
             continue
         sel = idx[t, :counts[t]]
         gref, lref = O.gradient_of(L, X[t], fi[sel], fl[sel])
-        assert abs(float(loss[t]) - lref) < 1e-4
+        assert abs(float(loss[t]) - lref) < (2e-3 if precision else 1e-4)
         errs = {key: rel(Gh[t, off:off + int(np.prod(shp))], gref[off:off + int(np.prod(shp))])
                 for key, shp, off in L.entries}
-        assert max(errs.values()) < 2e-4, (t, errs)
+        # against fp32 autograd the bf16 path shows the rounding of a random-init network (heavy cancellation) ...
+        assert max(errs.values()) < (1.5e-1 if precision else 2e-4), (t, errs)
+        assert not np.isnan(Gh[t, :L.P]).any()
+        if precision:
+            # ... against the same network with conv2's operands rounded to bf16 only accumulation order is left
+            gemu, lemu = O.gradient_of(L, X[t], fi[sel], fl[sel], emulate_bf16=True)
+            assert abs(float(loss[t]) - lemu) < 1e-4
+            errs = {key: rel(Gh[t, off:off + int(np.prod(shp))], gemu[off:off + int(np.prod(shp))])
+                    for key, shp, off in L.entries}
+            assert max(errs.values()) < 5e-3, (t, errs)
 
 
+@pytest.mark.parametrize("precision", [0, 1])
 @pytest.mark.parametrize("mu", [0.0, 0.9])
-def test_train_wave_vs_oracle(cuda, data, mu):
+def test_train_wave_vs_oracle(cuda, data, mu, precision):
     imgs, labs = data
     n, n_i, steps, B = 3, 48, 3, 32                      # 48 samples: steps of 32 + 16, third step empty
     X = rows(n, seed=3)
@@ -103,15 +118,16 @@ def test_train_wave_vs_oracle(cuda, data, mu):
                  torch.tensor(peers, dtype=torch.int32, device=cuda), torch.ones(n, dtype=torch.uint8, device=cuda),
                  torch.from_numpy(imgs.reshape(-1, 784)).to(cuda), torch.from_numpy(labs.reshape(-1)).to(cuda),
                  torch.from_numpy(np.ascontiguousarray(gidx.transpose(1, 0, 2))).to(cuda),
-                 torch.from_numpy(np.ascontiguousarray(cnt.T)).to(cuda), B, 0.004, mu, 0.0, K.Workspace(cuda))
+                 torch.from_numpy(np.ascontiguousarray(cnt.T)).to(cuda), B, 0.004, mu, 0.0, K.Workspace(cuda),
+                 precision=precision)
     torch.cuda.synchronize()
     Xg = Xd.cpu().numpy()
     for t in range(n):
         row, mom, _ = O.train_task(L, X[t], None, imgs[peers[t]], labs[peers[t]], idx[t], cnt[t], 0.004, mu, 0.0)
-        assert rel(Xg[t, :L.P], row[:L.P]) < 1e-5
-        assert rel(Xg[t, :L.P] - X[t, :L.P], row[:L.P] - X[t, :L.P]) < 1e-3
+        assert rel(Xg[t, :L.P], row[:L.P]) < (1e-4 if precision else 1e-5)     # north-star bound: 1e-3
+        assert rel(Xg[t, :L.P] - X[t, :L.P], row[:L.P] - X[t, :L.P]) < (2e-2 if precision else 1e-3)
         if mu:
-            assert rel(Md[peers[t], :L.P].cpu().numpy(), mom[:L.P]) < 1e-3
+            assert rel(Md[peers[t], :L.P].cpu().numpy(), mom[:L.P]) < (2e-2 if precision else 1e-3)
 
 
 def test_solver_dpsgd_femnist(cuda, tmp_path):

@@ -21,6 +21,14 @@ namespace fem {
 
 using gnl::Pass;
 using gnl::model_row;
+using gnl::SgdFuse;
+
+// fc1 on tensor cores (tc_fc.cu)
+int fc_nsp(int gs);
+int fc1_fwd_tc(const Pass &p, const uint16_t *a2k, float *h1, int w_off, int b_off, cudaStream_t st);
+int fc1_dgrad_tc(const Pass &p, const uint16_t *dh1k, float *da2, int w_off, cudaStream_t st);
+int fc1_wgrad_tc(const Pass &p, const uint16_t *a2k, const uint16_t *dh1k, const float *dh1, float *G, int64_t ldg,
+                 const SgdFuse &sgd, int w_off, int b_off, cudaStream_t st);
 
 constexpr int P = DLS_FEMNIST_P;
 constexpr int OFF_W1 = 0, OFF_B1 = 800, OFF_W2 = 832, OFF_B2 = 52032, OFF_FC1W = 52096, OFF_FC1B = 1657728,
@@ -40,6 +48,10 @@ struct Ws {
     // precision 1: bf16 planes [slot][C/8][RUNP14][8] (pixel r = y * 16 + x, gap pixels zero) + bf16 weight copies
     uint16_t *a1p, *dc2p, *zplane;
     void *prep_tc;
+    // fc1 operands (tc_fc.cu): a2k [node][392][nsp][8], dh1k [node][64][nsp][8] bf16, rows of missing samples zero
+    uint16_t *a2k, *dh1k;
+    int nsp;
+    SgdFuse sgd;                                        // optimizer step fused into the fc1 weight gradient (train waves)
     int tc;
 };
 constexpr int A1P_SZ = 4 * gnl::RUNP14 * 8, DC2P_SZ = 8 * gnl::RUNP14 * 8;      // bf16 elements per sample
@@ -64,6 +76,10 @@ static int64_t carve(Ws &ws, void *base, int n_groups, int gs, int n_models, boo
     ws.prep_tc = c.take<uint16_t>((int64_t)n_models * gnl::TC_PREP_ELEMS);
     ws.zplane = c.take<uint16_t>(gnl::RUNP15 * 8);
     ws.dc2p = backward ? c.take<uint16_t>(S * DC2P_SZ) : nullptr;
+    ws.nsp = fc_nsp(gs);
+    ws.a2k = c.take<uint16_t>((int64_t)n_groups * (FEAT / 8) * ws.nsp * 8);
+    ws.dh1k = backward ? c.take<uint16_t>((int64_t)n_groups * (HID / 8) * ws.nsp * 8) : nullptr;
+    ws.sgd = SgdFuse();
     ws.a1 = c.take<float>(S * A1_SZ);
     ws.c2 = c.take<float>(S * C2_SZ);
     ws.a2 = c.take<float>(S * A2_SZ);
@@ -164,8 +180,15 @@ conv1_relu_pool_kernel(Pass p, Ws ws, int save_bwd)
 __global__ void __launch_bounds__(256)
 relu_pool2_kernel(Pass p, Ws ws, int save_bwd)
 {
+    __shared__ __align__(16) __nv_bfloat16 sk[A2_SZ];      // the sample's features in flatten order, bf16 (tensor-core fc1)
     const int slot = blockIdx.x, t = threadIdx.x;
-    if (p.img_idx[slot] < 0) return;
+    const int g = slot / p.gs, sidx = slot - g * p.gs;
+    uint4 *a2k = ws.tc ? reinterpret_cast<uint4 *>(ws.a2k) + ((int64_t)g * (FEAT / 8)) * ws.nsp + sidx : nullptr;
+    if (p.img_idx[slot] < 0) {
+        if (a2k && p.gcount[g] > 0)
+            for (int e8 = t; e8 < FEAT / 8; e8 += 256) a2k[(int64_t)e8 * ws.nsp] = make_uint4(0u, 0u, 0u, 0u);
+        return;
+    }
     const float *src = ws.c2 + (int64_t)slot * C2_SZ;
     int m;
     const float *row = model_row(p, slot / p.gs, m);
@@ -182,6 +205,11 @@ relu_pool2_kernel(Pass p, Ws ws, int save_bwd)
         }
         ws.a2[(int64_t)slot * A2_SZ + c * 49 + pp] = best;
         if (save_bwd) ws.idx2[(int64_t)slot * A2_SZ + c * 49 + pp] = (uint8_t)bi;
+        if (a2k) sk[c * 49 + pp] = __float2bfloat16_rn(best);
+    }
+    if (a2k) {
+        __syncthreads();
+        for (int e8 = t; e8 < FEAT / 8; e8 += 256) a2k[(int64_t)e8 * ws.nsp] = reinterpret_cast<const uint4 *>(sk)[e8];
     }
 }
 
@@ -253,7 +281,7 @@ dense_fwd_kernel(const float *__restrict__ in, float *__restrict__ out, int out_
 template <int K, int N, bool MASK>
 __global__ void __launch_bounds__(256)
 dense_dgrad_kernel(const float *__restrict__ dout, int dout_stride, float *__restrict__ din,
-                   const float *__restrict__ act, Pass p, int w_off)
+                   const float *__restrict__ act, Pass p, int w_off, uint16_t *dk = nullptr, int nsp = 0)
 {
     constexpr int NT = 64;
     __shared__ __align__(16) float d_s[DLS_MAX_GROUP][NT];
@@ -295,10 +323,13 @@ dense_dgrad_kernel(const float *__restrict__ dout, int dout_stride, float *__res
             const int sl = s0 + s;
             if (sl >= gs) break;
             const int slot = g * gs + sl;
-            if (p.img_idx[slot] < 0) continue;
+            const bool live = p.img_idx[slot] >= 0;
             float v = acc[s];
-            if (MASK) v = act[(int64_t)slot * K + k] > 0.f ? v : 0.f;
-            din[(int64_t)slot * K + k] = v;
+            if (MASK) v = (live && act[(int64_t)slot * K + k] > 0.f) ? v : 0.f;
+            if (live) din[(int64_t)slot * K + k] = v;
+            if (dk)                                        // bf16 unit layout [node][k/8][nsp][8] (tc_fc.cu)
+                reinterpret_cast<__nv_bfloat16 *>(dk)[(((int64_t)g * (K / 8) + (k >> 3)) * nsp + sl) * 8 + (k & 7)] =
+                    __float2bfloat16_rn(live ? v : 0.f);
         }
     }
 }
@@ -457,45 +488,81 @@ bias2_grad_kernel(Pass p, Ws ws)
 }
 
 // conv1 weight/bias gradient: the gradient reaches conv1 only at the arg-max of each 2x2 window and
-// only where the pooled activation is positive.  grid = (groups, 4); warp = output channel,
-// lanes = the 25 taps.
+// only where the pooled activation is positive.  grid = (groups, 4); warp = output channel, lane = pooled
+// pixel (7 passes over the 196), all 25 taps of a thread accumulate in registers (one shared-memory read + one
+// FMA per tap; the lane-per-tap form spent 12 instructions per tap-row).  The next sample's gradients, arg-max
+// bytes and image are requested into registers while the current one is accumulated; the cross-lane sums run
+// once, at the end, in a fixed order.
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(Pass p, Ws ws)
 {
-    __shared__ float img[32 * 32];
-    __shared__ float gsl[196 * 8];
-    __shared__ uint8_t isl[196 * 8];
+    __shared__ float img[2][32 * 32];
+    __shared__ float red[8][26];
     const int g = blockIdx.x, chunk = blockIdx.y, t = threadIdx.x, lane = t & 31, w = t >> 5;
     if (p.gcount[g] <= 0) return;
-    for (int i = t; i < 1024; i += 256) img[i] = 0.f;
-    const int tap = lane < 25 ? lane : 0, off = (tap / 5) * 32 + tap % 5;
-    float acc = 0.f, bsum = 0.f;
+    for (int i = t; i < 2 * 1024; i += 256) (&img[0][0])[i] = 0.f;
+    const int co = chunk * 8 + w;
+    float acc[25], bsum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) acc[k] = 0.f;
+    float dv[7];
+    int iv[7];
+    uint32_t px4 = 0;
+    auto request = [&](int s) {                            // sample s -> registers (zeros when the slot is empty)
+        const int slot = g * p.gs + s, id = s < p.gs ? p.img_idx[slot] : -1;
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const int pp = q * 32 + lane;
+            dv[q] = 0.f; iv[q] = 0;
+            if (id >= 0 && pp < 196) {
+                const int64_t b = (int64_t)slot * A1_SZ + pp * 32 + co;
+                dv[q] = ws.a1[b] > 0.f ? ws.da1[b] : 0.f;
+                iv[q] = ws.idx1[b];
+            }
+        }
+        px4 = (id >= 0 && t < 196) ? reinterpret_cast<const uint32_t *>(p.images + (int64_t)id * IMG_BYTES)[t] : 0u;
+    };
+    request(0);
+    __syncthreads();
     for (int s = 0; s < p.gs; ++s) {
-        const int slot = g * p.gs + s, id = p.img_idx[slot];
-        if (id < 0) continue;
-        __syncthreads();
-        const uint8_t *src = p.images + (int64_t)id * IMG_BYTES;
-        for (int i = t; i < IMG_BYTES; i += 256) {
-            const int y = i / 28, x = i - y * 28;
-            img[(y + 2) * 32 + x + 2] = __fdiv_rn((float)src[i], 255.f);
+        float *im = img[s & 1];
+        if (t < 196) {
+            const int y = (4 * t) / 28, x = 4 * t - y * 28;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) im[(y + 2) * 32 + x + 2 + e] = __fdiv_rn((float)((px4 >> (8 * e)) & 0xffu), 255.f);
         }
-        for (int i = t; i < 196 * 8; i += 256) {
-            const int64_t b = (int64_t)slot * A1_SZ + (i >> 3) * 32 + chunk * 8 + (i & 7);
-            gsl[i] = ws.a1[b] > 0.f ? ws.da1[b] : 0.f;
-            isl[i] = ws.idx1[b];
-        }
+        float dc[7];
+        int ic[7];
+#pragma unroll
+        for (int q = 0; q < 7; ++q) { dc[q] = dv[q]; ic[q] = iv[q]; }
         __syncthreads();
-        for (int pp = 0; pp < 196; ++pp) {
-            const float d = gsl[pp * 8 + w];
-            const int ii = isl[pp * 8 + w], py = pp / 14, px = pp - py * 14;
-            acc = fmaf(d, img[(2 * py + (ii >> 1)) * 32 + 2 * px + (ii & 1) + off], acc);
-            bsum += d;
+        request(s + 1);
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const int pp = q * 32 + lane;
+            if (pp < 196 && dc[q] != 0.f) {
+                const int py = pp / 14, pxx = pp - py * 14;
+                const float *src = im + (2 * py + (ic[q] >> 1)) * 32 + 2 * pxx + (ic[q] & 1);
+                const float d = dc[q];
+#pragma unroll
+                for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+                    for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(d, src[ky * 32 + kx], acc[ky * 5 + kx]);
+                bsum += d;
+            }
         }
     }
+#pragma unroll
+    for (int k = 0; k < 25; ++k) {
+        const float v = warp_sum(acc[k]);
+        if (lane == 0) red[w][k] = v;
+    }
+    bsum = warp_sum(bsum);
+    if (lane == 0) red[w][25] = bsum;
+    __syncwarp();
     float *G = ws.G + (int64_t)g * ws.ldg;
-    const int co = chunk * 8 + w;
-    if (lane < 25) G[OFF_W1 + co * 25 + lane] = acc;
-    if (lane == 0) G[OFF_B1 + co] = bsum;
+    if (lane < 25) G[OFF_W1 + co * 25 + lane] = red[w][lane];
+    if (lane == 0) G[OFF_B1 + co] = red[w][25];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -525,6 +592,11 @@ static int forward(const Pass &p, Ws &ws, bool save, cudaStream_t st)
     prep_kernel<<<dim3(8, p.n_models), 256, 0, st>>>(p, ws.prep, p.gmodel ? nullptr : p.gcount);
     DLS_LAUNCH_CHECK();
     if (ws.tc && (rc = gnl::fem_prep_conv2_tc(p, ws.prep_tc, OFF_W2, save, st))) return rc;
+    if (ws.tc && ws.nsp != p.gs) {                        // sample rows gs..nsp-1 of the fc1 operands: zero
+        cudaError_t e = cudaMemsetAsync(ws.a2k, 0, (int64_t)p.n_groups * (FEAT / 8) * ws.nsp * 16, st);
+        if (e == cudaSuccess && ws.dh1k) e = cudaMemsetAsync(ws.dh1k, 0, (int64_t)p.n_groups * (HID / 8) * ws.nsp * 16, st);
+        if (e != cudaSuccess) return (int)e;
+    }
     conv1_relu_pool_kernel<<<S, 256, 0, st>>>(p, ws, sv);
     DLS_LAUNCH_CHECK();
     if (ws.tc) {
@@ -535,8 +607,12 @@ static int forward(const Pass &p, Ws &ws, bool save, cudaStream_t st)
     }
     relu_pool2_kernel<<<S, 256, 0, st>>>(p, ws, sv);
     DLS_LAUNCH_CHECK();
-    dense_fwd_kernel<FEAT, HID, true><<<dim3(p.n_groups, HID / 32), 256, 0, st>>>(ws.a2, ws.h1, HID, p, OFF_FC1W, OFF_FC1B);
-    DLS_LAUNCH_CHECK();
+    if (ws.tc) {
+        if ((rc = fc1_fwd_tc(p, ws.a2k, ws.h1, OFF_FC1W, OFF_FC1B, st))) return rc;
+    } else {
+        dense_fwd_kernel<FEAT, HID, true><<<dim3(p.n_groups, HID / 32), 256, 0, st>>>(ws.a2, ws.h1, HID, p, OFF_FC1W, OFF_FC1B);
+        DLS_LAUNCH_CHECK();
+    }
     dense_fwd_kernel<HID, NCLS, false><<<dim3(p.n_groups, 2), 256, 0, st>>>(ws.h1, ws.lg, 64, p, OFF_FC2W, OFF_FC2B);
     DLS_LAUNCH_CHECK();
     return 0;
@@ -547,12 +623,20 @@ static int backward(const Pass &p, Ws &ws, cudaStream_t st)
     const int S = p.n_groups * p.gs;
     dense_wgrad_kernel<HID, NCLS><<<dim3(p.n_groups, 2, HID / 128), 256, 0, st>>>(ws.lg, 64, ws.h1, p, ws.G, ws.ldg, OFF_FC2W, OFF_FC2B);
     DLS_LAUNCH_CHECK();
-    dense_dgrad_kernel<HID, NCLS, true><<<dim3(p.n_groups, HID / 128), 256, 0, st>>>(ws.lg, 64, ws.dh1, ws.h1, p, OFF_FC2W);
+    dense_dgrad_kernel<HID, NCLS, true><<<dim3(p.n_groups, HID / 128), 256, 0, st>>>(ws.lg, 64, ws.dh1, ws.h1, p, OFF_FC2W,
+                                                                                     ws.tc ? ws.dh1k : nullptr, ws.nsp);
     DLS_LAUNCH_CHECK();
-    dense_wgrad_kernel<FEAT, HID><<<dim3(p.n_groups, HID / 32, (FEAT + 127) / 128), 256, 0, st>>>(ws.dh1, HID, ws.a2, p, ws.G, ws.ldg, OFF_FC1W, OFF_FC1B);
-    DLS_LAUNCH_CHECK();
-    dense_dgrad_kernel<FEAT, HID, false><<<dim3(p.n_groups, (FEAT + 127) / 128), 256, 0, st>>>(ws.dh1, HID, ws.da2, nullptr, p, OFF_FC1W);
-    DLS_LAUNCH_CHECK();
+    if (ws.tc) {
+        // the data gradient reads the weights the fused optimizer step of the weight gradient overwrites: it goes first
+        int rc;
+        if ((rc = fc1_dgrad_tc(p, ws.dh1k, ws.da2, OFF_FC1W, st))) return rc;
+        if ((rc = fc1_wgrad_tc(p, ws.a2k, ws.dh1k, ws.dh1, ws.G, ws.ldg, ws.sgd, OFF_FC1W, OFF_FC1B, st))) return rc;
+    } else {
+        dense_wgrad_kernel<FEAT, HID><<<dim3(p.n_groups, HID / 32, (FEAT + 127) / 128), 256, 0, st>>>(ws.dh1, HID, ws.a2, p, ws.G, ws.ldg, OFF_FC1W, OFF_FC1B);
+        DLS_LAUNCH_CHECK();
+        dense_dgrad_kernel<FEAT, HID, false><<<dim3(p.n_groups, (FEAT + 127) / 128), 256, 0, st>>>(ws.dh1, HID, ws.da2, nullptr, p, OFF_FC1W);
+        DLS_LAUNCH_CHECK();
+    }
     pool2_bwd_kernel<<<S, 256, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     if (ws.tc) {
@@ -583,11 +667,12 @@ int64_t train_workspace_bytes(int n_tasks, int batch, bool own_G)
 }
 
 int step(const Pass &p, void *workspace, float *G, int64_t ldg, float *loss_out, float **G_used, int64_t *ldg_used,
-         int precision, cudaStream_t st)
+         int precision, const SgdFuse *sgd, cudaStream_t st)
 {
     Ws ws;
     carve(ws, workspace, p.n_groups, p.gs, p.n_models, true, G == nullptr);
     ws.tc = precision == 1;
+    if (sgd && ws.tc) ws.sgd = *sgd;
     if (G) { ws.G = G; ws.ldg = ldg; }
     int rc;
     if ((rc = forward(p, ws, true, st))) return rc;

@@ -5,7 +5,7 @@ namespace dls {
 namespace fem {
 int64_t train_workspace_bytes(int n_tasks, int batch, bool own_G);
 int step(const gnl::Pass &p, void *workspace, float *G, int64_t ldg, float *loss_out, float **G_used,
-         int64_t *ldg_used, int precision, cudaStream_t st);
+         int64_t *ldg_used, int precision, const gnl::SgdFuse *sgd, cudaStream_t st);
 int64_t eval_workspace_bytes(int n_models, int n_test);
 int eval(const float *X, int64_t ldx, const int32_t *model_rows, int n_models, const uint8_t *test_images,
          const int64_t *test_labels, int n_test, int32_t *out_correct, double *out_loss_sum, float *out_logits,
@@ -191,13 +191,31 @@ extern "C" int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int
             p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
             float *G = nullptr;
             int64_t ldg = 0;
+            // precision 1: the optimizer step of fc1.weight (95 % of P) happens in its weight-gradient epilogue
+            const bool fuse = precision == 1 && !tune_value(TUNE_NO_SGD_FUSE);
+            gnl::SgdFuse o;
+            if (fuse) {
+                o.X = X; o.ldx = ldx; o.M = M; o.ldm = ldm; o.task_row = task_row; o.task_peer = task_peer;
+                o.first = s == 0 ? mom_first : nullptr; o.lr = lr; o.mu = mu; o.wd = wd;
+            }
             if ((rcf = fem::step(p, workspace, nullptr, 0, loss_out ? loss_out + (int64_t)s * n_tasks : nullptr, &G,
-                                 &ldg, precision, stf)))
+                                 &ldg, precision, fuse ? &o : nullptr, stf)))
                 return rcf;
-            dim3 grid(128, n_tasks);
-            sgd_update_kernel<<<grid, 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
-                                                     s == 0 ? mom_first : nullptr, p.gcount, DLS_FEMNIST_P, lr, mu, wd, 0, 0);
-            DLS_LAUNCH_CHECK();
+            if (fuse) {
+                constexpr int F0 = 52096, F1 = 1657728;        // fc1.weight = [F0, F1) of the flat parameter row
+                sgd_update_kernel<<<dim3(8, n_tasks), 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
+                                                                     s == 0 ? mom_first : nullptr, p.gcount, F0, lr, mu, wd, 0, 0);
+                DLS_LAUNCH_CHECK();
+                sgd_update_kernel<<<dim3(8, n_tasks), 256, 0, stf>>>(X + F1, ldx, M ? M + F1 : nullptr, ldm, G + F1, ldg, task_row,
+                                                                     task_peer, s == 0 ? mom_first : nullptr, p.gcount,
+                                                                     DLS_FEMNIST_P - F1, lr, mu, wd, 0, 0);
+                DLS_LAUNCH_CHECK();
+            } else {
+                dim3 grid(128, n_tasks);
+                sgd_update_kernel<<<grid, 256, 0, stf>>>(X, ldx, M, ldm, G, ldg, task_row, task_peer,
+                                                         s == 0 ? mom_first : nullptr, p.gcount, DLS_FEMNIST_P, lr, mu, wd, 0, 0);
+                DLS_LAUNCH_CHECK();
+            }
         }
         return 0;
     }
@@ -307,7 +325,7 @@ extern "C" int dls_grad_wave(int32_t arch, const float *X, int64_t ldx, float *G
         gnl::Pass p;
         p.n_groups = n_tasks; p.gs = batch; p.n_models = n_tasks; p.gmodel = nullptr; p.mrow = task_row;
         p.img_idx = mb_index; p.gcount = mb_count; p.images = images; p.labels = labels; p.X = X; p.ldx = ldx;
-        return fem::step(p, workspace, G, ldg, loss_out, nullptr, nullptr, precision, (cudaStream_t)stream);
+        return fem::step(p, workspace, G, ldg, loss_out, nullptr, nullptr, precision, nullptr, (cudaStream_t)stream);
     }
     if (!task_row || !images || !labels || !mb_index || !mb_count || !workspace || n_tasks < 0)
         return DLS_E_ARG;

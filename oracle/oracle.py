@@ -162,13 +162,28 @@ def femnist_forward(p, x):
     return F.linear(x, p["fc2.weight"], p["fc2.bias"])
 
 
+class _LinearBf16(torch.autograd.Function):
+    """Dense layer as the precision-1 kernels compute it: every GEMM operand rounded to bf16, fp32 accumulation;
+    the bias gradient from the fp32 output gradient."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        return bf16r(x) @ bf16r(w).t() + b
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        return bf16r(dy) @ bf16r(w), bf16r(dy).t() @ bf16r(x), dy.sum(dim=0)
+
+
 def femnist_forward_bf16(p, x):
-    """FEMNIST CNN with conv2 evaluated like the precision-1 kernels (bf16 operands, fp32 accumulate, forward /
-    data gradient / weight gradient alike); conv1 and the dense layers stay fp32."""
+    """FEMNIST CNN with conv2 and fc1 evaluated like the precision-1 kernels (bf16 operands, fp32 accumulate,
+    forward / data gradient / weight gradient alike); conv1 and fc2 stay fp32."""
     x = F.max_pool2d(F.relu(F.conv2d(x, p["conv1.weight"], p["conv1.bias"], padding=2)), 2, 2)
     x = F.max_pool2d(F.relu(_ConvBf16.apply(x, p["conv2.weight"], p["conv2.bias"], True)), 2, 2)
     x = torch.flatten(x, 1)
-    x = F.relu(F.linear(x, p["fc1.weight"], p["fc1.bias"]))
+    x = F.relu(_LinearBf16.apply(x, p["fc1.weight"], p["fc1.bias"]))
     return F.linear(x, p["fc2.weight"], p["fc2.bias"])
 
 

@@ -32,7 +32,7 @@ int device_info(const DeviceInfo **out, int *dev_out = nullptr);
 int num_sms();
 
 // Experiment knobs set through dls_tune() (diagnostic entry point; 0 = automatic choice).
-enum TuneKey { TUNE_AGG_TW4 = 0, TUNE_AGG_STAGES = 1, TUNE_LANES = 2, TUNE_CONV_UNGROUPED = 3, TUNE_DEBUG = 4, TUNE_NO_SGD_FUSE = 5, TUNE_COUNT = 8 };
+enum TuneKey { TUNE_AGG_TW4 = 0, TUNE_AGG_STAGES = 1, TUNE_LANES = 2, TUNE_CONV_UNGROUPED = 3, TUNE_DEBUG = 4, TUNE_NO_SGD_FUSE = 5, TUNE_PUSH_CTAS = 6, TUNE_PUSH_MODE = 7, TUNE_COUNT = 8 };
 int tune_value(int key);
 
 // One-time, per-device opt-in to `bytes` of dynamic shared memory for `kernel`

@@ -460,31 +460,24 @@ pool2_bwd_kernel(Pass p, Ws ws)
 }
 
 // conv2 bias gradient (tensor-core path): every pooled position routes its gradient to exactly one conv2 pixel, so
-// db2[c] = sum over samples and pooled positions of da2 where the pooled activation is positive.  One CTA per node,
-// samples in slot order (deterministic).
+// db2[c] = sum over samples and pooled positions of da2 where the pooled activation is positive.  grid = (nodes, 8):
+// warp = channel, lane = pooled position (two passes over the 49), samples in slot order; fixed summation order.
 __global__ void __launch_bounds__(256)
 bias2_grad_kernel(Pass p, Ws ws)
 {
-    __shared__ float sm[A2_SZ];
-    const int g = blockIdx.x, t = threadIdx.x;
+    const int g = blockIdx.x, c = blockIdx.y * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (p.gcount[g] <= 0) return;
     float acc = 0.f;
     for (int s = 0; s < p.gs; ++s) {
         const int slot = g * p.gs + s;
         if (p.img_idx[slot] < 0) continue;
-        __syncthreads();
-        for (int i = t; i < A2_SZ; i += 256) {
-            const int64_t b = (int64_t)slot * A2_SZ + i;
-            sm[i] = ws.a2[b] > 0.f ? ws.da2[b] : 0.f;
-        }
-        __syncthreads();
-        if (t < 64) {
-            float a = 0.f;
-            for (int k = 0; k < 49; ++k) a += sm[t * 49 + k];
-            acc += a;
-        }
+        const int64_t b = (int64_t)slot * A2_SZ + c * 49;
+        float v = ws.a2[b + lane] > 0.f ? ws.da2[b + lane] : 0.f;
+        if (lane + 32 < 49) v += ws.a2[b + lane + 32] > 0.f ? ws.da2[b + lane + 32] : 0.f;
+        acc += v;
     }
-    if (t < 64) ws.G[(int64_t)g * ws.ldg + OFF_B2 + t] = acc;
+    acc = warp_sum(acc);
+    if (lane == 0) ws.G[(int64_t)g * ws.ldg + OFF_B2 + c] = acc;
 }
 
 // conv1 weight/bias gradient: the gradient reaches conv1 only at the arg-max of each 2x2 window and
@@ -496,11 +489,15 @@ bias2_grad_kernel(Pass p, Ws ws)
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(Pass p, Ws ws)
 {
-    __shared__ float img[2][32 * 32];
+    // row pitch 46: the lanes of a warp (consecutive pooled pixels, two image columns apart, rows 2 apart) then
+    // spread over the banks as 2 * pp (two-way conflicts at worst; pitch 32 puts the warp's three pixel rows on
+    // the same banks)
+    constexpr int IP = 46;
+    __shared__ float img[2][32 * IP];
     __shared__ float red[8][26];
     const int g = blockIdx.x, chunk = blockIdx.y, t = threadIdx.x, lane = t & 31, w = t >> 5;
     if (p.gcount[g] <= 0) return;
-    for (int i = t; i < 2 * 1024; i += 256) (&img[0][0])[i] = 0.f;
+    for (int i = t; i < 2 * 32 * IP; i += 256) (&img[0][0])[i] = 0.f;
     const int co = chunk * 8 + w;
     float acc[25], bsum = 0.f;
 #pragma unroll
@@ -529,7 +526,7 @@ conv1_wgrad_kernel(Pass p, Ws ws)
         if (t < 196) {
             const int y = (4 * t) / 28, x = 4 * t - y * 28;
 #pragma unroll
-            for (int e = 0; e < 4; ++e) im[(y + 2) * 32 + x + 2 + e] = __fdiv_rn((float)((px4 >> (8 * e)) & 0xffu), 255.f);
+            for (int e = 0; e < 4; ++e) im[(y + 2) * IP + x + 2 + e] = __fdiv_rn((float)((px4 >> (8 * e)) & 0xffu), 255.f);
         }
         float dc[7];
         int ic[7];
@@ -542,12 +539,12 @@ conv1_wgrad_kernel(Pass p, Ws ws)
             const int pp = q * 32 + lane;
             if (pp < 196 && dc[q] != 0.f) {
                 const int py = pp / 14, pxx = pp - py * 14;
-                const float *src = im + (2 * py + (ic[q] >> 1)) * 32 + 2 * pxx + (ic[q] & 1);
+                const float *src = im + (2 * py + (ic[q] >> 1)) * IP + 2 * pxx + (ic[q] & 1);
                 const float d = dc[q];
 #pragma unroll
                 for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
-                    for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(d, src[ky * 32 + kx], acc[ky * 5 + kx]);
+                    for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(d, src[ky * IP + kx], acc[ky * 5 + kx]);
                 bsum += d;
             }
         }
@@ -643,7 +640,7 @@ static int backward(const Pass &p, Ws &ws, cudaStream_t st)
         int rc;
         cudaError_t e = cudaMemsetAsync(ws.zplane, 0, gnl::RUNP15 * 16, st);
         if (e != cudaSuccess) return (int)e;
-        bias2_grad_kernel<<<p.n_groups, 256, 0, st>>>(p, ws);
+        bias2_grad_kernel<<<dim3(p.n_groups, 8), 256, 0, st>>>(p, ws);
         DLS_LAUNCH_CHECK();
         if ((rc = gnl::fem_conv2_wgrad_tc(p, ws.a1p, ws.dc2p, ws.zplane, ws.G, ws.ldg, OFF_W2, st))) return rc;
         if ((rc = gnl::fem_conv2_dgrad_tc(p, ws.dc2p, ws.da1, ws.prep_tc, st))) return rc;

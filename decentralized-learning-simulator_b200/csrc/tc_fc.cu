@@ -29,13 +29,15 @@ __device__ __forceinline__ void ld_global_v8(const void *p, float (&r)[8]) {
                  : "l"(p) : "memory");
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
 // producer thread index: warps 0-3 and 5-7 convert weights (warp 4 issues the MMAs)
 constexpr int FC_THREADS = 256, FC_PROD = 224, FC_PROD_WARPS = 7;
 
 // ------------------------------------------------------------------------------------------
 // forward: one CTA = one node x 128 output features; K streamed in chunks of 64
 // ------------------------------------------------------------------------------------------
-constexpr int FW_KC = 64, FW_NST = 4, FW_A_ST = (FW_KC / 8) * 128 * 16;
+constexpr int FW_KC = 64, FW_NST = 4, FW_PF = 3, FW_A_ST = (FW_KC / 8) * 128 * 16;
 template <int NSP> struct FwCfg {
     static constexpr int B_ST = (FW_KC / 8) * NSP * 16, STAGE = FW_A_ST + B_ST, SMEM = FW_NST * STAGE + 128;
 };
@@ -105,6 +107,13 @@ fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ 
                 const int i = pt + j * FC_PROD;
                 if (i < 1024) tc::ld_global_nc_v8(src0 + (int64_t)(i & 127) * FEAT + (i >> 7) * 8, v[j]);
             }
+            if (c + FW_PF < NCHUNK) {                      // the chunk FW_PF ahead: into L2 now, so its loads see L2 latency
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    const int i = pt + j * FC_PROD;
+                    if (i < 1024) prefetch_l2(src0 + FW_PF * FW_KC + (int64_t)(i & 127) * FEAT + (i >> 7) * 8);
+                }
+            }
 #pragma unroll
             for (int j = 0; j < 5; ++j) {
                 const int i = pt + j * FC_PROD;
@@ -141,7 +150,7 @@ fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ 
 // ------------------------------------------------------------------------------------------
 // data gradient: one CTA = one node x 128 input features (k); the reduction runs over the 512 rows of W
 // ------------------------------------------------------------------------------------------
-constexpr int DG_NC = 32, DG_NST = 4, DG_A_ST = 16 * DG_NC * 16, DG_TILES = (FEAT + 127) / 128;
+constexpr int DG_NC = 32, DG_NST = 4, DG_PF = 3, DG_A_ST = 16 * DG_NC * 16, DG_TILES = (FEAT + 127) / 128;
 template <int NSP> struct DgCfg {
     static constexpr int B_ALL = (HID / 8) * NSP * 16, SMEM = B_ALL + DG_NST * DG_A_ST + 128;
 };
@@ -217,6 +226,13 @@ fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict
 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[j][e] = 0.f;
                 if (i < 512 && m8 < kvalid8) tc::ld_global_nc_v8(src0 + (int64_t)n * FEAT + m8 * 8, v[j]);
+            }
+            if (c + DG_PF < NCHUNK) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const int i = pt + j * FC_PROD, n = i & 31, m8 = i >> 5;
+                    if (i < 512 && m8 < kvalid8) prefetch_l2(src0 + (int64_t)(DG_PF * DG_NC + n) * FEAT + m8 * 8);
+                }
             }
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
@@ -337,6 +353,13 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
         const float lr = sgd.lr, mu = sgd.mu, wd = sgd.wd;
         for (int j = 0; j < WG_TILES; ++j) {
             const int cols = FEAT - j * WG_TN < WG_TN ? FEAT - j * WG_TN : WG_TN;
+            if (fused && j + 1 < WG_TILES) {               // next tile's row segment of X (and M) into L2
+                const int nc = FEAT - (j + 1) * WG_TN < WG_TN ? FEAT - (j + 1) * WG_TN : WG_TN;
+                for (int q = 0; q < nc; q += 32) {
+                    prefetch_l2(xr + (j + 1) * WG_TN + q);
+                    if (mr && !fst) prefetch_l2(mr + (j + 1) * WG_TN + q);
+                }
+            }
             tc::mbar_wait(tfull, (uint32_t)(j & 1));
             tc::fence_after_sync();
             for (int c0 = 0; c0 < cols; c0 += 32) {

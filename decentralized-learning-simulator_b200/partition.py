@@ -272,14 +272,25 @@ class DistributedSolver(BatchedSolver):
                 if recv_l[r]:
                     for (peer, tn, idx), slot in zip(recv_l[r], self._push_slots(me, recv_l[r])):
                         self._halo_of[(tn, idx)] = parity * ex.halo_cap + slot
-            send_slots, dst = [], []
+            # Transfer order = what the GPUs write at the same time (the push kernel sweeps the list front to back):
+            # destinations are taken round-robin starting from rank + 1, so at any moment every GPU is written by all
+            # its peers evenly.  Listing them by ascending rank instead makes every GPU write to rank 0 first, then
+            # rank 1, ...: measured on 8 B200s 345 GB/s per GPU against 700 GB/s in this order
+            # (scripts/push_bw.py, profiles/r02_halo_bandwidth_8gpu_*.json).
             row_bytes = ex.layout.ld * 4
-            for q in range(self.world):
+            per_dst = []
+            for k in range(1, self.world):
+                q = (me + k) % self.world
                 if send_l[q]:
                     base = ex.peer_x_ptrs[q] + (ex.halo_base + parity * ex.halo_cap) * row_bytes
-                    for (peer, tn, idx), slot in zip(send_l[q], self._push_slots(q, send_l[q])):
-                        send_slots.append(vs[(tn, idx)])
-                        dst.append(base + slot * row_bytes)
+                    per_dst.append([(vs[(tn, idx)], base + slot * row_bytes)
+                                    for (peer, tn, idx), slot in zip(send_l[q], self._push_slots(q, send_l[q]))])
+            send_slots, dst = [], []
+            for i in range(max((len(x) for x in per_dst), default=0)):
+                for x in per_dst:
+                    if i < len(x):
+                        send_slots.append(x[i][0])
+                        dst.append(x[i][1])
             self._level_xchg[level] = {"send_slots": send_slots, "dst_ptrs": dst, "n_recv": n_recv}
             self.max_halo = max(self.max_halo, n_recv)
             self.max_send = max(self.max_send, n_send)

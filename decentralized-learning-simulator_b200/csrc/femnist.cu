@@ -132,9 +132,12 @@ conv1_relu_pool_kernel(Pass p, Ws ws, int save_bwd)
     __shared__ float img[32 * 32];
     __shared__ float wsm[25 * 32];
     __shared__ float bsm[32];
+    __shared__ __align__(16) __nv_bfloat16 spl[A1P_SZ];    // the sample's bf16 planes (tensor-core conv2)
     const int slot = blockIdx.x, t = threadIdx.x;
     const int id = p.img_idx[slot];
     if (id < 0) return;
+    if (ws.tc)
+        for (int i = t; i < A1P_SZ / 8; i += 256) reinterpret_cast<uint4 *>(spl)[i] = make_uint4(0u, 0u, 0u, 0u);
     int m;
     const float *row = model_row(p, slot / p.gs, m);
     const float *w1t = ws.prep + (int64_t)m * PREP_STRIDE + PO_W1T;
@@ -165,14 +168,12 @@ conv1_relu_pool_kernel(Pass p, Ws ws, int save_bwd)
         }
         ws.a1[(int64_t)slot * A1_SZ + o] = best;
         if (save_bwd) ws.idx1[(int64_t)slot * A1_SZ + o] = (uint8_t)bi;
-        if (ws.tc)
-            reinterpret_cast<__nv_bfloat16 *>(ws.a1p)[(int64_t)slot * A1P_SZ + ((co >> 3) * gnl::RUNP14 + py * 16 + px) * 8 +
-                                                      (co & 7)] = __float2bfloat16_rn(best);
+        if (ws.tc) spl[((co >> 3) * gnl::RUNP14 + py * 16 + px) * 8 + (co & 7)] = __float2bfloat16_rn(best);
     }
-    if (ws.tc && t < 4 * 26) {                           // the two gap pixels after rows 0..12 of every plane
-        const int pl = t / 26, r = t - pl * 26;
-        reinterpret_cast<uint4 *>(ws.a1p + (int64_t)slot * A1P_SZ)[pl * gnl::RUNP14 + (r >> 1) * 16 + 14 + (r & 1)] =
-            make_uint4(0u, 0u, 0u, 0u);
+    if (ws.tc) {                                         // planes leave as coalesced 16-byte stores (gap pixels: zero)
+        __syncthreads();
+        uint4 *dst = reinterpret_cast<uint4 *>(ws.a1p + (int64_t)slot * A1P_SZ);
+        for (int i = t; i < 4 * gnl::RUNP14; i += 256) dst[i] = reinterpret_cast<const uint4 *>(spl)[i];
     }
 }
 
@@ -189,28 +190,50 @@ relu_pool2_kernel(Pass p, Ws ws, int save_bwd)
             for (int e8 = t; e8 < FEAT / 8; e8 += 256) a2k[(int64_t)e8 * ws.nsp] = make_uint4(0u, 0u, 0u, 0u);
         return;
     }
-    const float *src = ws.c2 + (int64_t)slot * C2_SZ;
+    // results are staged in shared memory in flatten order [c][49] and leave as coalesced 16-byte stores (written
+    // straight from the channel-fastest compute order they are 4-byte stores 196 bytes apart)
+    __shared__ __align__(16) float sf[A2_SZ];
+    __shared__ __align__(16) uint8_t si[A2_SZ];
+    const float *__restrict__ src = ws.c2 + (int64_t)slot * C2_SZ;
     int m;
     const float *row = model_row(p, slot / p.gs, m);
-    for (int o = t; o < A2_SZ; o += 256) {
-        const int c = o & 63, pp = o >> 6, py = pp / 7, px = pp - py * 7;
-        const float bias = ws.tc ? row[OFF_B2 + c] : 0.f;   // the tensor-core convolution leaves the bias to its consumer
-        float best = -INFINITY;
-        int bi = 0;
+    const float bias = ws.tc ? row[OFF_B2 + (t & 63)] : 0.f;   // the tensor-core convolution leaves the bias to its consumer
+    constexpr int U = 4;
+    for (int o0 = t; o0 < A2_SZ; o0 += U * 256) {            // c = o & 63 is the same for all of a thread's outputs
+        float v[U][4];
 #pragma unroll
-        for (int d = 0; d < 4; ++d) {
-            float v = src[((2 * py + (d >> 1)) * 14 + 2 * px + (d & 1)) * 64 + c] + bias;
-            v = v > 0.f ? v : 0.f;
-            if (v > best) { best = v; bi = d; }
+        for (int u = 0; u < U; ++u) {
+            const int o = o0 + u * 256, pp = o >> 6, py = pp / 7, px = pp - py * 7;
+#pragma unroll
+            for (int d = 0; d < 4; ++d)
+                v[u][d] = o < A2_SZ ? __ldg(src + ((2 * py + (d >> 1)) * 14 + 2 * px + (d & 1)) * 64 + (o & 63)) : 0.f;
         }
-        ws.a2[(int64_t)slot * A2_SZ + c * 49 + pp] = best;
-        if (save_bwd) ws.idx2[(int64_t)slot * A2_SZ + c * 49 + pp] = (uint8_t)bi;
-        if (a2k) sk[c * 49 + pp] = __float2bfloat16_rn(best);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int o = o0 + u * 256, c = o & 63, pp = o >> 6;
+            if (o >= A2_SZ) break;
+            float best = -INFINITY;
+            int bi = 0;
+#pragma unroll
+            for (int d = 0; d < 4; ++d) {
+                float x = v[u][d] + bias;
+                x = x > 0.f ? x : 0.f;
+                if (x > best) { best = x; bi = d; }
+            }
+            sf[c * 49 + pp] = best;
+            si[c * 49 + pp] = (uint8_t)bi;
+            if (a2k) sk[c * 49 + pp] = __float2bfloat16_rn(best);
+        }
     }
-    if (a2k) {
-        __syncthreads();
+    __syncthreads();
+    float4 *a2o = reinterpret_cast<float4 *>(ws.a2 + (int64_t)slot * A2_SZ);
+    for (int i = t; i < A2_SZ / 4; i += 256) a2o[i] = reinterpret_cast<const float4 *>(sf)[i];
+    if (save_bwd) {
+        uint4 *io = reinterpret_cast<uint4 *>(ws.idx2 + (int64_t)slot * A2_SZ);
+        for (int i = t; i < A2_SZ / 16; i += 256) io[i] = reinterpret_cast<const uint4 *>(si)[i];
+    }
+    if (a2k)
         for (int e8 = t; e8 < FEAT / 8; e8 += 256) a2k[(int64_t)e8 * ws.nsp] = reinterpret_cast<const uint4 *>(sk)[e8];
-    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -480,45 +503,57 @@ bias2_grad_kernel(Pass p, Ws ws)
     if (lane == 0) ws.G[(int64_t)g * ws.ldg + OFF_B2 + c] = acc;
 }
 
-// conv1 weight/bias gradient: the gradient reaches conv1 only at the arg-max of each 2x2 window and
-// only where the pooled activation is positive.  grid = (groups, 4); warp = output channel, lane = pooled
-// pixel (7 passes over the 196), all 25 taps of a thread accumulate in registers (one shared-memory read + one
-// FMA per tap; the lane-per-tap form spent 12 instructions per tap-row).  The next sample's gradients, arg-max
-// bytes and image are requested into registers while the current one is accumulated; the cross-lane sums run
-// once, at the end, in a fixed order.
-__global__ void __launch_bounds__(256)
+// conv1 weight/bias gradient: the gradient reaches conv1 only at the arg-max of each 2x2 window and only where the
+// pooled activation is positive.  One CTA per node; lane = output channel, the 8 warps share the 196 pooled pixels
+// of a sample.  For a pooled pixel the 32 channels read the image at only four places (their arg-max positions
+// (dy, dx)), and with a row pitch of 34 floats those four addresses — offsets 0, 1, 34, 35 — lie in four different
+// banks: every one of the 25 tap reads is a single conflict-free (multicast) wavefront for all 32 channels, and the
+// gradients / arg-max bytes are plain coalesced 128-byte loads from [pixel][channel], requested one whole sample
+// ahead (a sample's accumulation takes about one DRAM latency; five-pixel batches left the kernel latency bound at
+// 480 us per 128-node launch, pixel-per-lane forms were bound by bank conflicts and 32-sector loads at 435 us; this
+// form: 210 us).  Per-warp partial sums are combined once, in a fixed order.
+constexpr int C1W_WARPS = 8;
+__global__ void __launch_bounds__(32 * C1W_WARPS)
 conv1_wgrad_kernel(Pass p, Ws ws)
 {
-    // row pitch 46: the lanes of a warp (consecutive pooled pixels, two image columns apart, rows 2 apart) then
-    // spread over the banks as 2 * pp (two-way conflicts at worst; pitch 32 puts the warp's three pixel rows on
-    // the same banks)
-    constexpr int IP = 46;
+    constexpr int IP = 34;
     __shared__ float img[2][32 * IP];
-    __shared__ float red[8][26];
-    const int g = blockIdx.x, chunk = blockIdx.y, t = threadIdx.x, lane = t & 31, w = t >> 5;
+    __shared__ float part[C1W_WARPS][26][32];
+    const int g = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
     if (p.gcount[g] <= 0) return;
-    for (int i = t; i < 2 * 32 * IP; i += 256) (&img[0][0])[i] = 0.f;
-    const int co = chunk * 8 + w;
+    for (int i = t; i < 2 * 32 * IP; i += 32 * C1W_WARPS) (&img[0][0])[i] = 0.f;
     float acc[25], bsum = 0.f;
 #pragma unroll
     for (int k = 0; k < 25; ++k) acc[k] = 0.f;
-    float dv[7];
-    int iv[7];
-    uint32_t px4 = 0;
-    auto request = [&](int s) {                            // sample s -> registers (zeros when the slot is empty)
-        const int slot = g * p.gs + s, id = s < p.gs ? p.img_idx[slot] : -1;
+    auto load_img = [&](int s) -> uint32_t {
+        const int id = s < p.gs ? p.img_idx[g * p.gs + s] : -1;
+        return (id >= 0 && t < 196) ? reinterpret_cast<const uint32_t *>(p.images + (int64_t)id * IMG_BYTES)[t] : 0u;
+    };
+    // the warp's pooled pixels are pp = w + 8 k, k = 0..24; a whole sample's gradients and arg-max bytes are requested
+    // one SAMPLE ahead (both loads unconditional): the accumulation of a sample takes about as long as one DRAM latency
+    constexpr int NK = (196 + C1W_WARPS - 1) / C1W_WARPS;  // 25
+    float dn[NK];
+    uint32_t in[(NK + 15) / 16];                           // 2 bits per pixel
+    auto request = [&](int s) {
+        const int slot = g * p.gs + s;
+        const bool live = s < p.gs && p.img_idx[slot] >= 0;
+        const float *a1s = ws.a1 + (int64_t)slot * A1_SZ + lane, *da1s = ws.da1 + (int64_t)slot * A1_SZ + lane;
+        const uint8_t *ixs = ws.idx1 + (int64_t)slot * A1_SZ + lane;
 #pragma unroll
-        for (int q = 0; q < 7; ++q) {
-            const int pp = q * 32 + lane;
-            dv[q] = 0.f; iv[q] = 0;
-            if (id >= 0 && pp < 196) {
-                const int64_t b = (int64_t)slot * A1_SZ + pp * 32 + co;
-                dv[q] = ws.a1[b] > 0.f ? ws.da1[b] : 0.f;
-                iv[q] = ws.idx1[b];
+        for (int q = 0; q < (NK + 15) / 16; ++q) in[q] = 0u;
+#pragma unroll
+        for (int k = 0; k < NK; ++k) {
+            const int pp = w + C1W_WARPS * k;
+            dn[k] = 0.f;
+            if (live && pp < 196) {
+                const float a = a1s[pp * 32], dd = da1s[pp * 32];
+                const uint32_t ix = ixs[pp * 32];
+                dn[k] = a > 0.f ? dd : 0.f;
+                in[k >> 4] |= (ix & 3u) << (2 * (k & 15));
             }
         }
-        px4 = (id >= 0 && t < 196) ? reinterpret_cast<const uint32_t *>(p.images + (int64_t)id * IMG_BYTES)[t] : 0u;
     };
+    uint32_t px4 = load_img(0);
     request(0);
     __syncthreads();
     for (int s = 0; s < p.gs; ++s) {
@@ -528,38 +563,43 @@ conv1_wgrad_kernel(Pass p, Ws ws)
 #pragma unroll
             for (int e = 0; e < 4; ++e) im[(y + 2) * IP + x + 2 + e] = __fdiv_rn((float)((px4 >> (8 * e)) & 0xffu), 255.f);
         }
-        float dc[7];
-        int ic[7];
+        float dc[NK];
+        uint32_t ic[(NK + 15) / 16];
 #pragma unroll
-        for (int q = 0; q < 7; ++q) { dc[q] = dv[q]; ic[q] = iv[q]; }
-        __syncthreads();
+        for (int k = 0; k < NK; ++k) dc[k] = dn[k];
+#pragma unroll
+        for (int q = 0; q < (NK + 15) / 16; ++q) ic[q] = in[q];
+        __syncthreads();                                   // image s visible; everyone is done with image s - 1
+        px4 = load_img(s + 1);
         request(s + 1);
 #pragma unroll
-        for (int q = 0; q < 7; ++q) {
-            const int pp = q * 32 + lane;
-            if (pp < 196 && dc[q] != 0.f) {
-                const int py = pp / 14, pxx = pp - py * 14;
-                const float *src = im + (2 * py + (ic[q] >> 1)) * IP + 2 * pxx + (ic[q] & 1);
-                const float d = dc[q];
+        for (int k = 0; k < NK; ++k) {
+            const int pp = w + C1W_WARPS * k;
+            if (pp >= 196) break;                          // warp-uniform
+            const int py = pp / 14, pxx = pp - py * 14;
+            const uint32_t ii = (ic[k >> 4] >> (2 * (k & 15))) & 3u;
+            const float *src = im + (2 * py + (int)(ii >> 1)) * IP + 2 * pxx + (int)(ii & 1u);
+            const float d = dc[k];
 #pragma unroll
-                for (int ky = 0; ky < 5; ++ky)
+            for (int ky = 0; ky < 5; ++ky)
 #pragma unroll
-                    for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(d, src[ky * IP + kx], acc[ky * 5 + kx]);
-                bsum += d;
-            }
+                for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] = fmaf(d, src[ky * IP + kx], acc[ky * 5 + kx]);
+            bsum += d;
         }
     }
 #pragma unroll
-    for (int k = 0; k < 25; ++k) {
-        const float v = warp_sum(acc[k]);
-        if (lane == 0) red[w][k] = v;
-    }
-    bsum = warp_sum(bsum);
-    if (lane == 0) red[w][25] = bsum;
-    __syncwarp();
+    for (int k = 0; k < 25; ++k) part[w][k][lane] = acc[k];
+    part[w][25][lane] = bsum;
+    __syncthreads();
     float *G = ws.G + (int64_t)g * ws.ldg;
-    if (lane < 25) G[OFF_W1 + co * 25 + lane] = red[w][lane];
-    if (lane == 0) G[OFF_B1 + co] = red[w][25];
+    for (int i = t; i < 26 * 32; i += 32 * C1W_WARPS) {
+        const int k = i >> 5, co = i & 31;
+        float v = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < C1W_WARPS; ++ww) v += part[ww][k][co];
+        if (k < 25) G[OFF_W1 + co * 25 + k] = v;
+        else G[OFF_B1 + co] = v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -652,7 +692,7 @@ static int backward(const Pass &p, Ws &ws, cudaStream_t st)
         gnl::conv5_kernel<64, 32, 14, false><<<S, 256, 18 * 18 * 64 * 4, st>>>(ws.dc2, ws.da1, p, ws.prep, PREP_STRIDE, PO_W2D, 0);
         DLS_LAUNCH_CHECK();
     }
-    conv1_wgrad_kernel<<<dim3(p.n_groups, 4), 256, 0, st>>>(p, ws);
+    conv1_wgrad_kernel<<<p.n_groups, 32 * C1W_WARPS, 0, st>>>(p, ws);
     DLS_LAUNCH_CHECK();
     return 0;
 }

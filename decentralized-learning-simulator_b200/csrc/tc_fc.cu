@@ -29,28 +29,36 @@ __device__ __forceinline__ void ld_global_v8(const void *p, float (&r)[8]) {
                  : "l"(p) : "memory");
 }
 
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
-
-// producer thread index: warps 0-3 and 5-7 convert weights (warp 4 issues the MMAs)
-constexpr int FC_THREADS = 256, FC_PROD = 224, FC_PROD_WARPS = 7;
+// Weight streaming (forward, data gradient): warps 0-3 load fp32 weights (256-bit loads, eight per thread in
+// flight), convert and store the bf16 UMMA layout; warp 4 issues the MMAs (and the bulk copies of B).  Small CTAs,
+// several per SM, because a converter warp waits out one DRAM latency per chunk.  Item -> (row, 32-byte unit)
+// mapping: the 8 lanes of a quarter-warp take 8 DIFFERENT rows — the destination (unit * rows + row) * 16 puts equal
+// row mod 8 on the same banks, and a 128-bit store is processed per quarter-warp — so the stores are conflict-free
+// and a warp instruction reads 8 rows x 128 contiguous bytes.
+// Tried and dropped (measured on the 128-node FEMNIST wave, whole round): rows fetched by bulk (TMA-engine) copies —
+// about 60 SM cycles per copy whatever its size, 256-byte rows move at 4 B/clk per SM (12.8 ms against 11.7 ms);
+// 16-byte LDGSTS copies into a private fp32 ring (two half-used sectors per item, 12.0 ms); L2 prefetch of the next
+// chunk (slower).  A probe that only reads the matrix in this pattern reaches 6.3 TB/s (scripts/probes/dram_runs.cu).
+constexpr int FC_THREADS = 160, FC_CONV = 128, FC_CONV_WARPS = 4;
 
 // ------------------------------------------------------------------------------------------
 // forward: one CTA = one node x 128 output features; K streamed in chunks of 64
 // ------------------------------------------------------------------------------------------
-constexpr int FW_KC = 64, FW_NST = 4, FW_PF = 3, FW_A_ST = (FW_KC / 8) * 128 * 16;
+constexpr int FW_KC = 64, FW_NB = 2, FW_A_ST = (FW_KC / 8) * 128 * 16;
 template <int NSP> struct FwCfg {
-    static constexpr int B_ST = (FW_KC / 8) * NSP * 16, STAGE = FW_A_ST + B_ST, SMEM = FW_NST * STAGE + 128;
+    static constexpr int B_ST = (FW_KC / 8) * NSP * 16, STAGE = FW_A_ST + B_ST, SMEM = FW_NB * STAGE + 128;
 };
 
 template <int NSP>
-__global__ void __launch_bounds__(FC_THREADS, 2)
+__global__ void __launch_bounds__(FC_THREADS, 4)
 fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ h1, int w_off, int b_off)
 {
     using C = FwCfg<NSP>;
     constexpr int NCHUNK = FEAT / FW_KC;                                 // 49
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + FW_NST * C::STAGE);
-    uint64_t *full = bars, *empty = bars + FW_NST, *done = bars + 2 * FW_NST;
+    uint8_t *sS = smem;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sS + FW_NB * C::STAGE);
+    uint64_t *bfull = bars, *bempty = bfull + FW_NB, *done = bempty + FW_NB;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(done + 1);
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int mt = blockIdx.x, g = blockIdx.y;
@@ -59,7 +67,7 @@ fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ 
     const float *row = model_row(p, g, m);
     const float *W = row + w_off + (int64_t)mt * 128 * FEAT;
     if (t == 0) {
-        for (int i = 0; i < FW_NST; ++i) { tc::mbar_init(&full[i], FC_PROD_WARPS + 1); tc::mbar_init(&empty[i], 1); }
+        for (int i = 0; i < FW_NB; ++i) { tc::mbar_init(&bfull[i], FC_CONV_WARPS + 1); tc::mbar_init(&bempty[i], 1); }
         tc::mbar_init(done, 1);
         tc::mbar_fence_init();
     }
@@ -72,73 +80,72 @@ fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ 
     if (warp == 4) {
         const bool leader = tc::elect_one();
         const uint32_t idesc = tc::instr_desc_bf16(128, NSP, 0, 0);
+        auto fetch_b = [&](int c) {
+            const int sb = c % FW_NB;
+            tc::mbar_expect_tx(&bfull[sb], (uint32_t)C::B_ST);
+            tc::bulk_g2s(tc::smem_u32(sS + sb * C::STAGE + FW_A_ST), a2k + ((int64_t)g * NK8 + c * (FW_KC / 8)) * (NSP * 8),
+                         (uint32_t)C::B_ST, &bfull[sb]);
+        };
+        if (leader)
+            for (int c = 0; c < FW_NB && c < NCHUNK; ++c) fetch_b(c);
+        __syncwarp();
         for (int c = 0; c < NCHUNK; ++c) {
-            const int b = c % FW_NST;
-            tc::mbar_wait(&full[b], (uint32_t)((c / FW_NST) & 1));
+            const int b = c % FW_NB;
+            tc::mbar_wait(&bfull[b], (uint32_t)((c / FW_NB) & 1));
             tc::fence_after_sync();
-            const uint32_t a_base = tc::smem_u32(smem + b * C::STAGE), b_base = a_base + FW_A_ST;
+            const uint32_t a_base = tc::smem_u32(sS + b * C::STAGE), b_base = a_base + FW_A_ST;
             if (leader) {
 #pragma unroll
                 for (int ks = 0; ks < FW_KC / 16; ++ks)
                     tc::mma_f16(tmem, tc::smem_desc(a_base + ks * 2 * 2048, 2048, 128),
                                 tc::smem_desc(b_base + ks * 2 * NSP * 16, NSP * 16, 128), idesc, (c | ks) != 0 ? 1u : 0u);
-                tc::mma_commit(&empty[b]);
+                tc::mma_commit(&bempty[b]);
+                if (c + FW_NB < NCHUNK) {                               // B of chunk c + NB goes where these MMAs read
+                    tc::mbar_wait(&bempty[b], (uint32_t)((c / FW_NB) & 1));
+                    fetch_b(c + FW_NB);
+                }
             }
             __syncwarp();
         }
         if (leader) tc::mma_commit(done);
         __syncwarp();
     } else {
-        const int pt = t < 128 ? t : t - 32;
+        auto item_n = [](int i) { return ((i >> 6) << 3) | (i & 7); };
+        auto item_k8 = [](int i) { return (((i >> 5) & 1) << 2) | ((i >> 3) & 3); };
         for (int c = 0; c < NCHUNK; ++c) {
-            const int b = c % FW_NST;
-            if (c >= FW_NST) tc::mbar_wait(&empty[b], (uint32_t)(((c / FW_NST) - 1) & 1));
-            uint8_t *sA = smem + b * C::STAGE;
-            if (warp == 5 && tc::elect_one()) {
-                tc::mbar_expect_tx(&full[b], (uint32_t)C::B_ST);
-                tc::bulk_g2s(tc::smem_u32(sA + FW_A_ST), a2k + ((int64_t)g * NK8 + c * (FW_KC / 8)) * (NSP * 8), (uint32_t)C::B_ST,
-                             &full[b]);
-            }
-            __syncwarp();
+            const int sb = c % FW_NB;
             const float *src0 = W + c * FW_KC;
-            float v[5][8];
+            float v[8][8];
 #pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                const int i = pt + j * FC_PROD;
-                if (i < 1024) tc::ld_global_nc_v8(src0 + (int64_t)(i & 127) * FEAT + (i >> 7) * 8, v[j]);
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j * FC_CONV;
+                tc::ld_global_nc_v8(src0 + (int64_t)item_n(i) * FEAT + item_k8(i) * 8, v[j]);
             }
-            if (c + FW_PF < NCHUNK) {                      // the chunk FW_PF ahead: into L2 now, so its loads see L2 latency
+            if (c >= FW_NB) tc::mbar_wait(&bempty[sb], (uint32_t)(((c / FW_NB) - 1) & 1));
+            uint8_t *sA = sS + sb * C::STAGE;
 #pragma unroll
-                for (int j = 0; j < 5; ++j) {
-                    const int i = pt + j * FC_PROD;
-                    if (i < 1024) prefetch_l2(src0 + FW_PF * FW_KC + (int64_t)(i & 127) * FEAT + (i >> 7) * 8);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                const int i = pt + j * FC_PROD;
-                if (i < 1024) *reinterpret_cast<uint4 *>(sA + ((i >> 7) * 128 + (i & 127)) * 16) = tc::pack8_bf16(v[j]);
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j * FC_CONV;
+                *reinterpret_cast<uint4 *>(sA + (item_k8(i) * 128 + item_n(i)) * 16) = tc::pack8_bf16(v[j]);
             }
             tc::fence_async_smem();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&full[b]);
+            if (lane == 0) tc::mbar_arrive(&bfull[sb]);
         }
-        if (warp < 4) {
-            tc::mbar_wait(done, 0);
-            tc::fence_after_sync();
-            uint32_t r[NSP];
+        tc::mbar_wait(done, 0);
+        tc::fence_after_sync();
+        uint32_t r[NSP];
 #pragma unroll
-            for (int c0 = 0; c0 < NSP; c0 += 16)
-                tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[16]>(&r[c0]));
-            tc::tmem_ld_wait();
-            const int n = mt * 128 + warp * 32 + lane;
-            const float bias = row[b_off + n];
+        for (int c0 = 0; c0 < NSP; c0 += 16)
+            tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[16]>(&r[c0]));
+        tc::tmem_ld_wait();
+        const int n = mt * 128 + warp * 32 + lane;
+        const float bias = row[b_off + n];
 #pragma unroll
-            for (int s = 0; s < NSP; ++s) {
-                if (s < p.gs && p.img_idx[g * p.gs + s] >= 0) {
-                    const float x = __uint_as_float(r[s]) + bias;
-                    h1[(int64_t)(g * p.gs + s) * HID + n] = x > 0.f ? x : 0.f;
-                }
+        for (int s = 0; s < NSP; ++s) {
+            if (s < p.gs && p.img_idx[g * p.gs + s] >= 0) {
+                const float x = __uint_as_float(r[s]) + bias;
+                h1[(int64_t)(g * p.gs + s) * HID + n] = x > 0.f ? x : 0.f;
             }
         }
     }
@@ -150,21 +157,21 @@ fc1_fwd_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, float *__restrict__ 
 // ------------------------------------------------------------------------------------------
 // data gradient: one CTA = one node x 128 input features (k); the reduction runs over the 512 rows of W
 // ------------------------------------------------------------------------------------------
-constexpr int DG_NC = 32, DG_NST = 4, DG_PF = 3, DG_A_ST = 16 * DG_NC * 16, DG_TILES = (FEAT + 127) / 128;
+constexpr int DG_NC = 64, DG_NB = 2, DG_A_ST = 16 * DG_NC * 16, DG_TILES = (FEAT + 127) / 128;
 template <int NSP> struct DgCfg {
-    static constexpr int B_ALL = (HID / 8) * NSP * 16, SMEM = B_ALL + DG_NST * DG_A_ST + 128;
+    static constexpr int B_ALL = (HID / 8) * NSP * 16, SMEM = B_ALL + DG_NB * DG_A_ST + 128;
 };
 
 template <int NSP>
-__global__ void __launch_bounds__(FC_THREADS, 2)
+__global__ void __launch_bounds__(FC_THREADS, 3)
 fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict__ da2, int w_off)
 {
     using C = DgCfg<NSP>;
-    constexpr int NCHUNK = HID / DG_NC;                                  // 16
+    constexpr int NCHUNK = HID / DG_NC;                                  // 8
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *sB = smem, *sA0 = smem + C::B_ALL;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sA0 + DG_NST * DG_A_ST);
-    uint64_t *full = bars, *empty = bars + DG_NST, *done = bars + 2 * DG_NST, *bbar = done + 1;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sA0 + DG_NB * DG_A_ST);
+    uint64_t *bfull = bars, *bempty = bfull + DG_NB, *done = bempty + DG_NB, *bbar = done + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bbar + 1);
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
     const int kt = blockIdx.x, g = blockIdx.y, k0 = kt * 128;
@@ -174,7 +181,7 @@ fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict
     const float *W = row + w_off + k0;
     const int kvalid8 = (FEAT - k0 < 128 ? FEAT - k0 : 128) / 8;         // 16-byte units of a row segment that exist
     if (t == 0) {
-        for (int i = 0; i < DG_NST; ++i) { tc::mbar_init(&full[i], FC_PROD_WARPS); tc::mbar_init(&empty[i], 1); }
+        for (int i = 0; i < DG_NB; ++i) { tc::mbar_init(&bfull[i], FC_CONV_WARPS); tc::mbar_init(&bempty[i], 1); }
         tc::mbar_init(done, 1);
         tc::mbar_init(bbar, 1);
         tc::mbar_fence_init();
@@ -196,8 +203,8 @@ fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict
         const uint32_t idesc = tc::instr_desc_bf16(128, NSP, 1, 0);
         const uint32_t b_base = tc::smem_u32(sB);
         for (int c = 0; c < NCHUNK; ++c) {
-            const int b = c % DG_NST;
-            tc::mbar_wait(&full[b], (uint32_t)((c / DG_NST) & 1));
+            const int b = c % DG_NB;
+            tc::mbar_wait(&bfull[b], (uint32_t)((c / DG_NB) & 1));
             tc::fence_after_sync();
             const uint32_t a_base = tc::smem_u32(sA0 + b * DG_A_ST);
             if (leader) {
@@ -206,57 +213,49 @@ fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict
                     tc::mma_f16(tmem, tc::smem_desc(a_base + ks * 256, 128, DG_NC * 16),
                                 tc::smem_desc(b_base + (c * (DG_NC / 16) + ks) * 2 * NSP * 16, NSP * 16, 128), idesc,
                                 (c | ks) != 0 ? 1u : 0u);
-                tc::mma_commit(&empty[b]);
+                tc::mma_commit(&bempty[b]);
             }
             __syncwarp();
         }
         if (leader) tc::mma_commit(done);
         __syncwarp();
     } else {
-        const int pt = t < 128 ? t : t - 32;
+        auto item_n = [](int i) { return ((i >> 7) << 3) | (i & 7); };
+        auto item_m8 = [](int i) { return (((i >> 5) & 3) << 2) | ((i >> 3) & 3); };
         for (int c = 0; c < NCHUNK; ++c) {
-            const int b = c % DG_NST;
-            if (c >= DG_NST) tc::mbar_wait(&empty[b], (uint32_t)(((c / DG_NST) - 1) & 1));
-            uint8_t *sA = sA0 + b * DG_A_ST;
+            const int sb = c % DG_NB;
             const float *src0 = W + (int64_t)c * DG_NC * FEAT;
-            float v[3][8];
+            float v[8][8];
 #pragma unroll
-            for (int j = 0; j < 3; ++j) {
-                const int i = pt + j * FC_PROD, n = i & 31, m8 = i >> 5;
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j * FC_CONV, m8 = item_m8(i);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[j][e] = 0.f;
-                if (i < 512 && m8 < kvalid8) tc::ld_global_nc_v8(src0 + (int64_t)n * FEAT + m8 * 8, v[j]);
+                if (m8 < kvalid8) tc::ld_global_nc_v8(src0 + (int64_t)item_n(i) * FEAT + m8 * 8, v[j]);
             }
-            if (c + DG_PF < NCHUNK) {
+            if (c >= DG_NB) tc::mbar_wait(&bempty[sb], (uint32_t)(((c / DG_NB) - 1) & 1));
+            uint8_t *sA = sA0 + sb * DG_A_ST;
 #pragma unroll
-                for (int j = 0; j < 3; ++j) {
-                    const int i = pt + j * FC_PROD, n = i & 31, m8 = i >> 5;
-                    if (i < 512 && m8 < kvalid8) prefetch_l2(src0 + (int64_t)(DG_PF * DG_NC + n) * FEAT + m8 * 8);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 3; ++j) {
-                const int i = pt + j * FC_PROD;
-                if (i < 512) *reinterpret_cast<uint4 *>(sA + ((i >> 5) * DG_NC + (i & 31)) * 16) = tc::pack8_bf16(v[j]);
+            for (int j = 0; j < 8; ++j) {
+                const int i = t + j * FC_CONV;
+                *reinterpret_cast<uint4 *>(sA + (item_m8(i) * DG_NC + item_n(i)) * 16) = tc::pack8_bf16(v[j]);
             }
             tc::fence_async_smem();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&full[b]);
+            if (lane == 0) tc::mbar_arrive(&bfull[sb]);
         }
-        if (warp < 4) {
-            tc::mbar_wait(done, 0);
-            tc::fence_after_sync();
-            uint32_t r[NSP];
+        tc::mbar_wait(done, 0);
+        tc::fence_after_sync();
+        uint32_t r[NSP];
 #pragma unroll
-            for (int c0 = 0; c0 < NSP; c0 += 16)
-                tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[16]>(&r[c0]));
-            tc::tmem_ld_wait();
-            const int k = k0 + warp * 32 + lane;
-            if (k < FEAT) {
+        for (int c0 = 0; c0 < NSP; c0 += 16)
+            tc::tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, *reinterpret_cast<uint32_t(*)[16]>(&r[c0]));
+        tc::tmem_ld_wait();
+        const int k = k0 + warp * 32 + lane;
+        if (k < FEAT) {
 #pragma unroll
-                for (int s = 0; s < NSP; ++s)
-                    if (s < p.gs && p.img_idx[g * p.gs + s] >= 0) da2[(int64_t)(g * p.gs + s) * FEAT + k] = __uint_as_float(r[s]);
-            }
+            for (int s = 0; s < NSP; ++s)
+                if (s < p.gs && p.img_idx[g * p.gs + s] >= 0) da2[(int64_t)(g * p.gs + s) * FEAT + k] = __uint_as_float(r[s]);
         }
     }
     tc::fence_before_sync();
@@ -267,12 +266,15 @@ fc1_dgrad_tc_kernel(Pass p, const uint16_t *__restrict__ dh1k, float *__restrict
 // ------------------------------------------------------------------------------------------
 // weight gradient (+ optimizer step): one CTA = one node x 128 output features; 25 tiles of 128 columns (k)
 // ------------------------------------------------------------------------------------------
-constexpr int WG_THREADS_FC = 160, WG_TN = 128, WG_TILES = (FEAT + WG_TN - 1) / WG_TN, WG_NST = 3;
+// the 25 column tiles of a (node, 128 features) pair are split over WG_ZS CTAs: 512 CTAs of 25 tiles are 1.15 waves
+// of the 444 resident CTAs (the second wave is a tail of 68), 2560 CTAs of 5 tiles are 5.8
+constexpr int WG_THREADS_FC = 160, WG_TN = 128, WG_TILES = (FEAT + WG_TN - 1) / WG_TN, WG_NST = 3, WG_ZS = 5, WG_TPC = WG_TILES / WG_ZS;
+static_assert(WG_TPC * WG_ZS == WG_TILES, "tiles split evenly");
 template <int NSP> struct WgCfg {
     static constexpr int A_BYTES = 16 * NSP * 16, B_ST = (WG_TN / 8) * NSP * 16, SMEM = A_BYTES + WG_NST * B_ST + 128;
 };
 
-template <int NSP>
+template <int NSP, bool MOM>
 __global__ void __launch_bounds__(WG_THREADS_FC, 3)
 fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__restrict__ dh1k,
                     const float *__restrict__ dh1, float *__restrict__ G, int64_t ldg, SgdFuse sgd, int w_off, int b_off)
@@ -284,7 +286,7 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
     uint64_t *bfull = bars, *bempty = bars + WG_NST, *tfull = bars + 2 * WG_NST, *tempty = tfull + 1, *abar = tempty + 1;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(abar + 1);
     const int t = threadIdx.x, warp = tc::uniform_warp_idx(), lane = t & 31;
-    const int mt = blockIdx.x, g = blockIdx.y;
+    const int mt = blockIdx.x, g = blockIdx.y, j0 = blockIdx.z * WG_TPC, j1 = j0 + WG_TPC;
     if (p.gcount[g] <= 0) return;
     if (t == 0) {
         for (int i = 0; i < WG_NST; ++i) { tc::mbar_init(&bfull[i], 1); tc::mbar_init(&bempty[i], 1); }
@@ -302,22 +304,22 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
         auto fetch = [&](int j) {                                        // tile j of a2k -> stage j % WG_NST
             const int cols8 = (FEAT - j * WG_TN < WG_TN ? FEAT - j * WG_TN : WG_TN) / 8;
             const uint32_t bytes = (uint32_t)(cols8 * NSP * 16);
-            tc::mbar_expect_tx(&bfull[j % WG_NST], bytes);
-            tc::bulk_g2s(tc::smem_u32(sB0 + (j % WG_NST) * C::B_ST), a2k + ((int64_t)g * NK8 + j * (WG_TN / 8)) * (NSP * 8), bytes,
-                         &bfull[j % WG_NST]);
+            tc::mbar_expect_tx(&bfull[(j - j0) % WG_NST], bytes);
+            tc::bulk_g2s(tc::smem_u32(sB0 + ((j - j0) % WG_NST) * C::B_ST), a2k + ((int64_t)g * NK8 + j * (WG_TN / 8)) * (NSP * 8),
+                         bytes, &bfull[(j - j0) % WG_NST]);
         };
         if (leader) {
             tc::mbar_expect_tx(abar, (uint32_t)C::A_BYTES);
             tc::bulk_g2s(tc::smem_u32(sA), dh1k + ((int64_t)g * (HID / 8) + mt * 16) * (NSP * 8), (uint32_t)C::A_BYTES, abar);
-            for (int j = 0; j < WG_NST && j < WG_TILES; ++j) fetch(j);
+            for (int j = j0; j < j0 + WG_NST && j < j1; ++j) fetch(j);
         }
         __syncwarp();
         tc::mbar_wait(abar, 0);
         const uint32_t a_base = tc::smem_u32(sA);
-        for (int j = 0; j < WG_TILES; ++j) {
-            const int b = j % WG_NST;
-            tc::mbar_wait(&bfull[b], (uint32_t)((j / WG_NST) & 1));
-            if (j > 0) tc::mbar_wait(tempty, (uint32_t)((j - 1) & 1));
+        for (int j = j0; j < j1; ++j) {
+            const int b = (j - j0) % WG_NST;
+            tc::mbar_wait(&bfull[b], (uint32_t)(((j - j0) / WG_NST) & 1));
+            if (j > j0) tc::mbar_wait(tempty, (uint32_t)((j - j0 - 1) & 1));
             tc::fence_after_sync();
             const int cols = FEAT - j * WG_TN < WG_TN ? FEAT - j * WG_TN : WG_TN;
             const uint32_t idesc = tc::instr_desc_bf16(128, cols, 1, 1);
@@ -329,8 +331,8 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
                                 idesc, ks != 0 ? 1u : 0u);
                 tc::mma_commit(tfull);
                 tc::mma_commit(&bempty[b]);
-                if (j + WG_NST < WG_TILES) {
-                    tc::mbar_wait(&bempty[b], (uint32_t)((j / WG_NST) & 1));
+                if (j + WG_NST < j1) {
+                    tc::mbar_wait(&bempty[b], (uint32_t)(((j - j0) / WG_NST) & 1));
                     fetch(j + WG_NST);
                 }
             }
@@ -338,7 +340,7 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
         }
     } else {
         const int n = mt * 128 + warp * 32 + lane;
-        {   // fc1 bias gradient from the fp32 dh1 rows (sample order)
+        if (blockIdx.z == 0) {   // fc1 bias gradient from the fp32 dh1 rows (sample order)
             float bsum = 0.f;
             for (int s = 0; s < p.gs; ++s)
                 if (p.img_idx[g * p.gs + s] >= 0) bsum += dh1[(int64_t)(g * p.gs + s) * HID + n];
@@ -347,28 +349,57 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
         const bool fused = sgd.X != nullptr;
         float *xr = fused ? sgd.X + (int64_t)sgd.task_row[g] * sgd.ldx + w_off + (int64_t)n * FEAT
                           : G + (int64_t)g * ldg + w_off + (int64_t)n * FEAT;
-        float *mr = (fused && sgd.M && sgd.mu != 0.f) ? sgd.M + (int64_t)sgd.task_peer[g] * sgd.ldm + w_off + (int64_t)n * FEAT
-                                                      : nullptr;
+        float *mr = MOM ? sgd.M + (int64_t)sgd.task_peer[g] * sgd.ldm + w_off + (int64_t)n * FEAT : nullptr;   // MOM implies fused
         const bool fst = (fused && sgd.first) ? (sgd.first[g] != 0) : false;
         const float lr = sgd.lr, mu = sgd.mu, wd = sgd.wd;
-        for (int j = 0; j < WG_TILES; ++j) {
+        for (int j = j0; j < j1; ++j) {
             const int cols = FEAT - j * WG_TN < WG_TN ? FEAT - j * WG_TN : WG_TN;
-            if (fused && j + 1 < WG_TILES) {               // next tile's row segment of X (and M) into L2
-                const int nc = FEAT - (j + 1) * WG_TN < WG_TN ? FEAT - (j + 1) * WG_TN : WG_TN;
-                for (int q = 0; q < nc; q += 32) {
-                    prefetch_l2(xr + (j + 1) * WG_TN + q);
-                    if (mr && !fst) prefetch_l2(mr + (j + 1) * WG_TN + q);
-                }
-            }
-            tc::mbar_wait(tfull, (uint32_t)(j & 1));
+            tc::mbar_wait(tfull, (uint32_t)((j - j0) & 1));
             tc::fence_after_sync();
+            if (!MOM) {
+                // no momentum row: 64 columns (256 B of the row) requested per pass, consumed in two TMEM reads
+                for (int c0 = 0; c0 < cols; c0 += 64) {
+                    const int k = j * WG_TN + c0;
+                    float pv[64];
+                    if (fused) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) ld_global_v8(xr + k + q * 8, *reinterpret_cast<float(*)[8]>(&pv[q * 8]));
+                    }
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t r[32];
+                        tc::tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c0 + 32 * h), r);
+                        tc::tmem_ld_wait();
+                        if (h == 1 && c0 + 64 >= cols) {                 // accumulator free for the next tile
+                            tc::fence_before_sync();
+                            tc::mbar_arrive(tempty);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            float gv = __uint_as_float(r[i]);
+                            if (fused) {
+                                const float x = pv[32 * h + i];
+                                if (wd != 0.f) gv = fmaf(wd, x, gv);
+                                gv = fmaf(-lr, gv, x);
+                            }
+                            pv[32 * h + i] = gv;
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            tc::st_global_v8(xr + k + 32 * h + q * 8, pv[32 * h + q * 8], pv[32 * h + q * 8 + 1],
+                                             pv[32 * h + q * 8 + 2], pv[32 * h + q * 8 + 3], pv[32 * h + q * 8 + 4],
+                                             pv[32 * h + q * 8 + 5], pv[32 * h + q * 8 + 6], pv[32 * h + q * 8 + 7]);
+                    }
+                }
+                continue;
+            }
             for (int c0 = 0; c0 < cols; c0 += 32) {
                 const int k = j * WG_TN + c0;
                 float pv[32], mv[32];
-                if (fused) {                                             // the row segment's loads go out before the TMEM read
+                {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) ld_global_v8(xr + k + q * 8, *reinterpret_cast<float(*)[8]>(&pv[q * 8]));
-                    if (mr && !fst) {
+                    if (!fst) {
 #pragma unroll
                         for (int q = 0; q < 4; ++q) ld_global_v8(mr + k + q * 8, *reinterpret_cast<float(*)[8]>(&mv[q * 8]));
                     }
@@ -380,31 +411,20 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
                     tc::fence_before_sync();
                     tc::mbar_arrive(tempty);
                 }
-                float o[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     float gv = __uint_as_float(r[i]);
-                    if (fused) {
-                        if (wd != 0.f) gv = fmaf(wd, pv[i], gv);
-                        if (mr) {
-                            const float bv = fst ? gv : __fadd_rn(__fmul_rn(mv[i], mu), gv);
-                            mv[i] = bv;
-                            gv = bv;
-                        }
-                        o[i] = fmaf(-lr, gv, pv[i]);
-                    } else {
-                        o[i] = gv;
-                    }
+                    if (wd != 0.f) gv = fmaf(wd, pv[i], gv);
+                    const float bv = fst ? gv : __fadd_rn(__fmul_rn(mv[i], mu), gv);
+                    mv[i] = bv;
+                    pv[i] = fmaf(-lr, bv, pv[i]);
                 }
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    tc::st_global_v8(xr + k + q * 8, o[q * 8], o[q * 8 + 1], o[q * 8 + 2], o[q * 8 + 3], o[q * 8 + 4], o[q * 8 + 5],
-                                     o[q * 8 + 6], o[q * 8 + 7]);
-                if (mr) {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        tc::st_global_v8(mr + k + q * 8, mv[q * 8], mv[q * 8 + 1], mv[q * 8 + 2], mv[q * 8 + 3], mv[q * 8 + 4],
-                                         mv[q * 8 + 5], mv[q * 8 + 6], mv[q * 8 + 7]);
+                for (int q = 0; q < 4; ++q) {
+                    tc::st_global_v8(xr + k + q * 8, pv[q * 8], pv[q * 8 + 1], pv[q * 8 + 2], pv[q * 8 + 3], pv[q * 8 + 4],
+                                     pv[q * 8 + 5], pv[q * 8 + 6], pv[q * 8 + 7]);
+                    tc::st_global_v8(mr + k + q * 8, mv[q * 8], mv[q * 8 + 1], mv[q * 8 + 2], mv[q * 8 + 3], mv[q * 8 + 4],
+                                     mv[q * 8 + 5], mv[q * 8 + 6], mv[q * 8 + 7]);
                 }
             }
         }
@@ -443,11 +463,17 @@ template <int NSP>
 static int wgrad_launch(const Pass &p, const uint16_t *a2k, const uint16_t *dh1k, const float *dh1, float *G, int64_t ldg,
                         const SgdFuse &sgd, int w_off, int b_off, cudaStream_t st)
 {
-    static PerDeviceOnce attr;
-    int rc = ensure_dyn_smem(fc1_wgrad_tc_kernel<NSP>, WgCfg<NSP>::SMEM, attr);
-    if (rc) return rc;
-    fc1_wgrad_tc_kernel<NSP><<<dim3(HID / 128, p.n_groups), WG_THREADS_FC, WgCfg<NSP>::SMEM, st>>>(p, a2k, dh1k, dh1, G, ldg, sgd,
-                                                                                             w_off, b_off);
+    static PerDeviceOnce attr, attr_m;
+    const dim3 grid(HID / 128, p.n_groups, WG_ZS);
+    if (sgd.X && sgd.M && sgd.mu != 0.f) {
+        int rc = ensure_dyn_smem(fc1_wgrad_tc_kernel<NSP, true>, WgCfg<NSP>::SMEM, attr_m);
+        if (rc) return rc;
+        fc1_wgrad_tc_kernel<NSP, true><<<grid, WG_THREADS_FC, WgCfg<NSP>::SMEM, st>>>(p, a2k, dh1k, dh1, G, ldg, sgd, w_off, b_off);
+    } else {
+        int rc = ensure_dyn_smem(fc1_wgrad_tc_kernel<NSP, false>, WgCfg<NSP>::SMEM, attr);
+        if (rc) return rc;
+        fc1_wgrad_tc_kernel<NSP, false><<<grid, WG_THREADS_FC, WgCfg<NSP>::SMEM, st>>>(p, a2k, dh1k, dh1, G, ldg, sgd, w_off, b_off);
+    }
     DLS_LAUNCH_CHECK();
     return 0;
 }

@@ -12,7 +12,7 @@ def main():
     rows = [r for r in csv.reader(open(path, errors="replace")) if len(r) > 10 and r[0] != "ID"]
     launches = collections.OrderedDict()
     for r in rows:
-        d = launches.setdefault(int(r[0]), {"name": r[4]})
+        d = launches.setdefault(int(r[0]), {"name": r[4], "grid": r[8].replace(" ", "")})
         try:
             d[r[12]] = float(r[14].replace(",", ""))
         except ValueError:
@@ -43,7 +43,7 @@ def main():
     agg_traffic = sum(v.get("dram__bytes_read.sum", 0) + v.get("dram__bytes_write.sum", 0) for v in aggs) / max(1, len(aggs))
     by = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0])
     for v in ours:
-        b = by[short(v["name"])]
+        b = by[short(v["name"]) + " " + v["grid"]]          # train and test waves launch the same kernels on different grids
         b[0] += 1; b[1] += v["gpu__time_duration.sum"]
         b[2] += v.get("dram__bytes_read.sum", 0); b[3] += v.get("dram__bytes_write.sum", 0)
     tot = sum(b[1] for b in by.values())

@@ -47,8 +47,9 @@ int64_t     dls_launch_count(void);
  * pipeline stages, 2 = number of equal lanes a train wave is split into, 3 = 1: round-1 tensor-core convolution
  * kernels (one MMA per tap, fp32 activations converted by producer warps) instead of the plane / bulk-copy /
  * tap-pair kernels, 5 = 1: separate optimizer kernel for the whole row instead of the update fused into the
- * weight-gradient kernels; value 0 restores the default.  Process-wide, not thread-safe, never needed for correct
- * results.  No reference counterpart. */
+ * weight-gradient kernels, 6 = CTAs per SM of dls_push_rows, 7 = dls_push_rows kernel form (0: 16-byte accesses,
+ * grid-stride; 1: 32-byte accesses; 2: persistent CTAs sweeping the transfer list front to back); value 0 restores the
+ * default.  Process-wide, not thread-safe, never needed for correct results.  No reference counterpart. */
 int         dls_tune(int32_t key, int32_t value);
 
 /* ------------------------------------------------------------------------------------------
@@ -110,7 +111,10 @@ int dls_broadcast_row(const float *src, float *Y, int64_t ldy, const int32_t *ds
  * transfer e copies X[src_rows[e], 0:P) to the row that starts at device address dst_ptrs[e], which may be
  * PEER memory mapped into this process (another GPU's halo rows).  Destinations must be 16-byte aligned and hold
  * at least ceil(P/4)*4 floats.  The kernel ends with a system-scope fence; the caller must run a cross-GPU
- * barrier on `stream` before any GPU reads the rows pushed to it.  At most 65535 transfers per call. */
+ * barrier on `stream` before any GPU reads the rows pushed to it.  At most 65535 transfers per call.  The kernel
+ * works through the list roughly front to back, so its ORDER decides which peers are written at the same time:
+ * interleave the destinations (round-robin starting at rank + 1) — sorted by destination, every GPU of a box writes
+ * to the same peer at once and the exchange runs at half the bandwidth (345 vs 700 GB/s per GPU on 8 B200s). */
 int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_rows, const uint64_t *dst_ptrs,
                   int32_t n_transfers, int64_t P, void *stream);
 
@@ -132,7 +136,8 @@ int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_rows, const ui
  *   loss_out      optional [n_steps][n_tasks] mean minibatch loss
  * Loss: NLL of log_softmax (GNLeNet) / cross entropy (FEMNIST), mean over the delivered batch.
  * Math: fp32 CUDA-core kernels when `precision == 0`; `precision == 1` uses bf16 tensor-core
- * operands with fp32 accumulation for the convolution GEMMs.
+ * operands with fp32 accumulation for the convolution GEMMs (GNLeNet: all three convolutions; FEMNIST: conv2 and the
+ * 3136x512 dense layer, whose optimizer step then happens inside its weight-gradient kernel).
  * ------------------------------------------------------------------------------------------ */
 int64_t dls_train_workspace_bytes(int32_t arch, int32_t n_tasks, int32_t batch);
 int dls_train_wave(int32_t arch, float *X, int64_t ldx, float *M, int64_t ldm,

@@ -110,11 +110,15 @@ extern "C" int dls_push_rows(const float *X, int64_t ldx, const int32_t *src_row
     if (bx > want) bx = want;
     if (bx < 1) bx = 1;
     dim3 grid((unsigned)bx, (unsigned)n_transfers);
-    if (dls::tune_value(dls::TUNE_PUSH_MODE) == 2 && (ldx & 7) == 0 && ((uintptr_t)X & 31) == 0) {
+    // Long rows (FEMNIST: 6.8 MB) are exchanged in column ranges that overlap with the aggregate of the previous range
+    // (partition.py): the persistent form with ONE CTA per SM moves the same 700 GB/s per GPU (scripts/push_bw.py) and
+    // leaves room on every SM for the aggregate kernel's CTA, where thousands of short-lived CTAs would run first.
+    const bool long_rows = P >= (1 << 18) && dls::tune_value(dls::TUNE_PUSH_MODE) == 0;
+    if ((long_rows || dls::tune_value(dls::TUNE_PUSH_MODE) == 2) && (ldx & 7) == 0 && ((uintptr_t)X & 31) == 0) {
         const int64_t P8 = (P + 7) / 8;
         const int pbx = (int)((P8 + dls::PUSH_BLOCK8 - 1) / dls::PUSH_BLOCK8);
         const int64_t n_items = (int64_t)pbx * n_transfers;
-        int64_t ctas = (int64_t)per_sm * sms;
+        int64_t ctas = (int64_t)(long_rows && dls::tune_value(dls::TUNE_PUSH_CTAS) <= 0 ? 1 : per_sm) * sms;
         if (ctas > n_items) ctas = n_items;
         dls::push_rows_persistent_kernel<<<(unsigned)ctas, 256, 0, (cudaStream_t)stream>>>(X, ldx, src_rows, dst_ptrs, P8, pbx,
                                                                                         n_items);

@@ -149,8 +149,13 @@ class WaveExecutor:
         hdl.barrier(channel=0)                                    # nobody pushes before every X is in place
         return True
 
-    def push_rows(self, slots_dev: torch.Tensor, dst_ptrs_dev: torch.Tensor):
-        K.push_rows(self.X, slots_dev, dst_ptrs_dev, self.layout.P)
+    def push_rows(self, slots_dev: torch.Tensor, dst_ptrs_dev: torch.Tensor, cols=None):
+        """`cols` = (first column, count): push only that column range of the rows (pipelined exchange)."""
+        if cols is None:
+            K.push_rows(self.X, slots_dev, dst_ptrs_dev, self.layout.P)
+        else:
+            c0, n = cols
+            K.push_rows(self.X[:, c0:c0 + n], slots_dev, dst_ptrs_dev + 4 * c0, n)
 
     def symm_barrier(self):
         self.symm.barrier(channel=0)
@@ -267,7 +272,7 @@ class WaveExecutor:
 
     def aggregate_wave(self, model_slots: Sequence[Sequence[int]], out_slots: Sequence[int],
                        weights: Optional[Sequence[Optional[Sequence[float]]]] = None, variant: int = 0,
-                       prepared=None):
+                       prepared=None, cols=None):
         """FedAvg for every task of the wave: `model_slots[r]` is task r's `models` list as slots
         in list order (dasklearn/gradient_aggregation/fedavg.py:12-26)."""
         if len(out_slots) == 0:
@@ -276,9 +281,17 @@ class WaveExecutor:
             prepared = self.prepare_aggregate(model_slots, out_slots, weights)
         rowptr, colidx, wval, src_rows, out_rows, n_src, hint = prepared
         # auto: the variant the library says fits this wave shape (settled in prepare_aggregate)
-        K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows,
-                   out_rows=out_rows, n_src_rows=n_src, variant=variant or hint["variant"])
-        self.stats["agg_rows"] += len(out_slots)
+        if cols is None:
+            K.agg_spmm(self.X, self.X, rowptr, colidx, wval, self.layout.P, src_rows=src_rows,
+                       out_rows=out_rows, n_src_rows=n_src, variant=variant or hint["variant"])
+            self.stats["agg_rows"] += len(out_slots)
+        else:                                                # a column range of the wave (pipelined exchange)
+            c0, n = cols
+            Xc = self.X[:, c0:c0 + n]
+            K.agg_spmm(Xc, Xc, rowptr, colidx, wval, n, src_rows=src_rows, out_rows=out_rows, n_src_rows=n_src,
+                       variant=variant or hint["variant"])
+            if c0 == 0:
+                self.stats["agg_rows"] += len(out_slots)
 
     def prepare_aggregate(self, model_slots, out_slots, weights=None):
         """CSR descriptors of an aggregate wave, built with array operations (a wave of 1024 tasks x fan-in 11

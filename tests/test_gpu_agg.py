@@ -191,3 +191,29 @@ def test_push_rows_to_device_addresses(cuda):
             assert torch.equal(H[b, :L.P], X[a, :L.P])
     untouched = [r for r in range(64) if r not in (7, *range(63, 63 - 14, -1))]
     assert bool(torch.isnan(H[untouched]).all())
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_push_rows_long_rows_and_column_ranges(cuda, mode):
+    """Rows of FEMNIST length take the persistent form of the push kernel (one CTA per SM); the pipelined exchange
+    pushes COLUMN RANGES of the rows (a view of X, destinations advanced by the same offset).  All kernel forms
+    (dls_tune key 7) must move exactly the requested bytes."""
+    from dls_b200 import _lib
+    from dls_b200.layout import FEMNIST as F
+    lib = _lib.lib()
+    X = torch.randn((5, F.ld), device=cuda)
+    H = torch.full((6, F.ld), float("nan"), device=cuda)
+    src, dst = [4, 0, 2], [1, 5, 3]
+    s = torch.tensor(src, dtype=torch.int32, device=cuda)
+    d = torch.tensor([H.data_ptr() + r * F.ld * 4 for r in dst], dtype=torch.int64, device=cuda)
+    cuts = [0, 425984, 847872, 1269760, F.P]
+    lib.dls_tune(7, mode)
+    try:
+        for c0, c1 in zip(cuts[:-1], cuts[1:]):
+            K.push_rows(X[:, c0:c1], s, d + 4 * c0, c1 - c0)
+        torch.cuda.synchronize()
+    finally:
+        lib.dls_tune(7, 0)
+    for a, b in zip(src, dst):
+        assert torch.equal(H[b, :F.P], X[a, :F.P])
+    assert bool(torch.isnan(H[[0, 2, 4]]).all())

@@ -108,13 +108,13 @@ static int64_t carve(Ws &ws, void *base, int n_groups, int gs, int n_models, boo
 
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-prep_kernel(Pass p, float *prep, const int32_t *model_active)
+prep_kernel(Pass p, float *prep, const int32_t *model_active, int limit)
 {
     const int m = blockIdx.y;
     if (model_active && model_active[m] == 0) return;
     const float *row = p.X + (int64_t)p.mrow[m] * p.ldx;
     float *dst = prep + (int64_t)m * PREP_STRIDE;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < PREP_STRIDE; i += gridDim.x * blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < limit; i += gridDim.x * blockDim.x) {
         float v;
         if (i < PO_W2T) { const int co = i & 31, tap = i >> 5; v = row[OFF_W1 + co * 25 + tap]; }
         else if (i < PO_W2D) { const int j = i - PO_W2T, co = j & 63, ci = (j >> 6) & 31, tap = j >> 11;
@@ -454,7 +454,18 @@ pool2_bwd_kernel(Pass p, Ws ws)
     const int slot = blockIdx.x, t = threadIdx.x;
     if (p.img_idx[slot] < 0) return;
     if (ws.tc) {
-        // bf16 planes: one 16-byte entry (8 channels of a pixel) per item, gap pixels zeroed
+        // bf16 planes: one 16-byte entry (8 channels of a pixel) per item, gap pixels zeroed.  The sample's masked
+        // pooled gradients and arg-max bytes are fetched once, coalesced, into shared memory (every pooled value is
+        // needed by the four pixels of its window, and the [c][49] layout is 196 bytes apart across channels)
+        __shared__ float sg[A2_SZ];
+        __shared__ uint8_t si[A2_SZ];
+        for (int i = t; i < A2_SZ; i += 256) {
+            const int64_t b = (int64_t)slot * A2_SZ + i;
+            const float a = ws.a2[b], d = ws.da2[b];
+            sg[i] = a > 0.f ? d : 0.f;
+            si[i] = ws.idx2[b];
+        }
+        __syncthreads();
         uint4 *dst = reinterpret_cast<uint4 *>(ws.dc2p + (int64_t)slot * DC2P_SZ);
         for (int i = t; i < 196 * 8; i += 256) {
             const int ch = i / 196, pix = i - ch * 196, y = pix / 14, x = pix - y * 14;
@@ -462,8 +473,8 @@ pool2_bwd_kernel(Pass p, Ws ws)
             float v[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-                const int64_t b = (int64_t)slot * A2_SZ + (ch * 8 + e) * 49 + (y >> 1) * 7 + (x >> 1);
-                v[e] = ((int)ws.idx2[b] == sel && ws.a2[b] > 0.f) ? ws.da2[b] : 0.f;
+                const int o = (ch * 8 + e) * 49 + (y >> 1) * 7 + (x >> 1);
+                v[e] = (int)si[o] == sel ? sg[o] : 0.f;
             }
             dst[ch * gnl::RUNP14 + y * 16 + x] = tc::pack8_bf16(v);
         }
@@ -626,7 +637,9 @@ static int forward(const Pass &p, Ws &ws, bool save, cudaStream_t st)
     int rc = set_attrs();
     if (rc) return rc;
     const int S = p.n_groups * p.gs, sv = save ? 1 : 0;
-    prep_kernel<<<dim3(8, p.n_models), 256, 0, st>>>(p, ws.prep, p.gmodel ? nullptr : p.gcount);
+    // tensor-core path: only conv1's transposed weights are needed in fp32 (conv2's operands are the bf16 copies)
+    prep_kernel<<<dim3(ws.tc ? 1 : 8, p.n_models), 256, 0, st>>>(p, ws.prep, p.gmodel ? nullptr : p.gcount,
+                                                              ws.tc ? PO_W2T : PREP_STRIDE);
     DLS_LAUNCH_CHECK();
     if (ws.tc && (rc = gnl::fem_prep_conv2_tc(p, ws.prep_tc, OFF_W2, save, st))) return rc;
     if (ws.tc && ws.nsp != p.gs) {                        // sample rows gs..nsp-1 of the fc1 operands: zero

@@ -356,7 +356,7 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
             const int cols = FEAT - j * WG_TN < WG_TN ? FEAT - j * WG_TN : WG_TN;
             tc::mbar_wait(tfull, (uint32_t)((j - j0) & 1));
             tc::fence_after_sync();
-            if (!MOM) {
+            if constexpr (!MOM) {
                 // no momentum row: 64 columns (256 B of the row) requested per pass, consumed in two TMEM reads
                 for (int c0 = 0; c0 < cols; c0 += 64) {
                     const int k = j * WG_TN + c0;
@@ -391,8 +391,7 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
                                              pv[32 * h + q * 8 + 5], pv[32 * h + q * 8 + 6], pv[32 * h + q * 8 + 7]);
                     }
                 }
-                continue;
-            }
+            } else {
             for (int c0 = 0; c0 < cols; c0 += 32) {
                 const int k = j * WG_TN + c0;
                 float pv[32], mv[32];
@@ -426,6 +425,7 @@ fc1_wgrad_tc_kernel(Pass p, const uint16_t *__restrict__ a2k, const uint16_t *__
                     tc::st_global_v8(mr + k + q * 8, mv[q * 8], mv[q * 8 + 1], mv[q * 8 + 2], mv[q * 8 + 3], mv[q * 8 + 4],
                                      mv[q * 8 + 5], mv[q * 8 + 6], mv[q * 8 + 7]);
                 }
+            }
             }
         }
     }

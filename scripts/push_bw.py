@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """Halo-exchange bandwidth on this box (run under torchrun, one rank per GPU): every rank sends ROWS rows of LD floats
 to every peer — the traffic pattern of one C3 aggregate level — through (1) NCCL all_to_all_single from a packed
-buffer, (2) dls_push_rows into symmetric memory, with the grid / access-width variants of dls_tune keys 6 / 7, and
-(3) one pair alone (rank 0 -> rank 1).  Prints one JSON line on rank 0: GB/s per GPU, outbound, max over ranks.
+buffer, (2) dls_push_rows into symmetric memory in three transfer-list orders (ascending destination rank, shifted =
+all of rank + 1 first, interleaved = round-robin over the destinations) x the kernel forms / CTA counts of dls_tune
+keys 6 / 7, and (3) one pair alone (rank 0 -> rank 1), by stores and by the copy engine.  Prints one JSON line on
+rank 0: GB/s per GPU, outbound, max over ranks.  Results: profiles/r02_halo_bandwidth_8gpu_*.json.
 
     python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 scripts/push_bw.py [ROWS] [LD]
 """
@@ -33,15 +35,6 @@ def main():
     X.normal_()
     ptrs = [int(p) for p in hdl.buffer_ptrs]
     peers = [p for p in range(world) if p != rank]
-    # transfer e: own row e -> peer's halo row (n_send + slot of this rank at the peer)
-    src, dst = [], []
-    for j, p in enumerate(peers):
-        my_index_at_peer = rank if rank < p else rank - 1
-        for r in range(rows_per_peer):
-            src.append(j * rows_per_peer + r)
-            dst.append(ptrs[p] + (n_send + my_index_at_peer * rows_per_peer + r) * ld * 4)
-    src_d = torch.tensor(src, dtype=torch.int32, device=dev)
-    dst_d = torch.tensor(dst, dtype=torch.int64, device=dev)
     bytes_out = n_send * ld * 4
 
     def timed(fn, iters=4):
@@ -60,7 +53,7 @@ def main():
     out = {"world": world, "rows_per_peer": rows_per_peer, "row_bytes": ld * 4, "bytes_out_per_gpu": bytes_out}
 
     def transfers(order):
-        src, dst = [], []
+        # transfer: own row (j-th peer, r) -> that peer's halo row (n_send + slot of this rank at the peer)
         items = []
         for j, p in enumerate(peers):
             my_index_at_peer = rank if rank < p else rank - 1

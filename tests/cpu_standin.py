@@ -98,3 +98,31 @@ class OracleExecutor(WaveExecutor):
             a, l, _ = O.evaluate(self.layout, self.X[s].numpy(), self.test_images, self.test_labels)
             acc.append(a); loss.append(l)
         return np.array(acc), np.array(loss)
+
+
+class PushOracleExecutor(OracleExecutor):
+    """Stand-in for the symmetric-memory push transport, all ranks as THREADS of one process: every rank's X is a
+    CPU tensor laid out like the symmetric allocation ([pool_cap pool rows | 2 x halo_cap halo rows]), the "peer
+    pointers" are the tensors' real addresses, a push is a memmove to the address the planner computed, and the
+    cross-GPU barrier is a threading.Barrier.  Exercises the planner's halo slot numbering, the two halo halves and
+    the transfer lists without a GPU."""
+
+    def setup_push(self, pool_cap, halo_cap, barrier):
+        X2 = torch.zeros((pool_cap + 2 * halo_cap, self.layout.ld), dtype=torch.float32)
+        X2[:self.n_slots] = self.X[:self.n_slots]
+        self.X = X2
+        self.symm = object()                       # symmetric mode: _grow stays inside the allocation, halo_base = pool_cap
+        self.pool_cap, self.halo_cap = pool_cap, halo_cap
+        self._barrier = barrier
+        self.transport = "push"
+        self.pushed_to = []                        # destination addresses in list order (what the test inspects)
+
+    def push_rows(self, slots_dev, dst_ptrs_dev, cols=None):
+        import ctypes
+        assert cols is None
+        for s, d in zip(slots_dev.tolist(), dst_ptrs_dev.tolist()):
+            ctypes.memmove(d, self.X[s].data_ptr(), self.layout.P * 4)
+            self.pushed_to.append(d)
+
+    def symm_barrier(self):
+        self._barrier.wait(timeout=120)
